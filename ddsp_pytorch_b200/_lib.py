@@ -1,0 +1,54 @@
+"""ctypes binding of libddsp_b200.so -- the only way this package reaches the GPU.
+
+There is deliberately no fallback: if the library is missing or a call fails, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from .build import LIB_PATH
+
+_p, _i, _u32, _u64, _sz = C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/ddsp_b200.h one to one (tests/test_abi.py checks it)
+SIGNATURES = {
+    "ddsp_abi_version": (_i, []),
+    "ddsp_last_error": (C.c_char_p, []),
+    "ddsp_osc_state_bytes": (_sz, [_i, _i, _i]),
+    "ddsp_osc_forward": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "ddsp_osc_backward_scratch_bytes": (_sz, [_i, _i, _i]),
+    "ddsp_osc_backward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ddsp_noise_forward": (_i, [_p, _p, _p, _i, _u64, _u32, _u32, _i, _i, _i, _i, _p]),
+    "ddsp_noise_backward": (_i, [_p, _p, _p, _u64, _u32, _u32, _i, _i, _i, _i, _p]),
+    "ddsp_noise_uniform": (_i, [_p, _u64, _u32, _u32, _i, _i, _i, _p]),
+    "ddsp_amp_to_impulse_response": (_i, [_p, _p, _i, _i, _i, _p]),
+    "ddsp_probe_fp32_fma": (_i, [_p, _i, _i, _i, _p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"ddsp_pytorch_b200: {LIB_PATH} is missing. Build it with `python -m ddsp_pytorch_b200.build` "
+                "(needs nvcc). There is no CPU or eager fallback for this path.")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)          # AttributeError if the library is stale
+            fn.restype, fn.argtypes = res, args
+        if lib.ddsp_abi_version() != 1:
+            raise RuntimeError("ddsp_pytorch_b200: libddsp_b200.so ABI version mismatch; rebuild it")
+        _lib = lib
+    return _lib
+
+
+def call(name: str, *args) -> None:
+    """Invoke an int-returning entry point and raise on a non-zero status."""
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed ({rc}): {lib.ddsp_last_error().decode()}")

@@ -1,0 +1,402 @@
+// Filtered-noise synthesiser for sm_100a -- replaces FilteredNoise.forward (filtered_noise.py:40-53).
+//
+// The reference runs, per frame, irfft(H) -> roll/Hann/pad/roll (amp_to_impulse_response, :7-22) and
+// then three FFTs of size 2*hop (fft_convolve, :25-32) on noise drawn by the CPU generator and copied
+// to the GPU (:44-48).  Here one CTA owns one frame end to end:
+//   * the M = 2(NB-1) tap zero-phase FIR is built in shared memory from the NB magnitudes by the
+//     real inverse DFT written out as a cosine sum (r is even, so only r[0..M/2] is needed),
+//     windowed with the periodic Hann;  after the reference's two rolls the filter is
+//         causal taps      hc[q] = r[q]     * 0.5(1+cos(2 pi q/M)),  q = 0..M/2-1   at lag q
+//         wrapped taps     ha[i] = r[M/2-i] * 0.5(1-cos(2 pi i/M)),  i = 0..M/2-1   at lag hop-M/2+i
+//   * the uniform noise is generated in-kernel (Philox4x32-10) or read from the caller,
+//   * the frame's causal, truncated convolution is done directly from shared memory with an
+//     8-output x 8-tap register tile (64 FFMA per 4 LDS.128) -- no overlap-add, tails dropped (:50-51).
+// The backward kernel regenerates the same noise, correlates it with the upstream gradient into the
+// tap gradients and applies the transposed cosine sum.
+#include "ddsp_common.cuh"
+
+namespace ddsp {
+
+struct NoiseSmem {
+    float* Hs;    // [NB]        magnitudes, later reused for d/dH accumulation
+    float* ct;    // [M]         cos(2 pi i / M)
+    float* rr;    // [M/2+1]     r = irfft(H)[0..M/2]
+    float* hc;    // [TP]        causal taps (zero padded to a multiple of 8)
+    float* ha;    // [TP]        wrapped (anti-causal) taps
+    float* u;     // [PADL + hop] noise with PADL leading zeros
+    int TP, PADL;
+};
+
+__host__ __device__ inline int noise_tp(int NB) { return ((NB - 1) + 7) & ~7; }
+
+__host__ __device__ inline size_t noise_smem_floats(int NB, int hop) {
+    const int M = 2 * (NB - 1), TP = noise_tp(NB);
+    size_t n = ((NB + 3) & ~3) + ((M + 3) & ~3) + ((M / 2 + 1 + 3) & ~3) + 2 * (size_t)TP + (TP + 8) + hop;
+    return n;
+}
+
+__device__ __forceinline__ NoiseSmem carve_noise_smem(float* base, int NB, int hop) {
+    const int M = 2 * (NB - 1);
+    NoiseSmem s;
+    s.TP = noise_tp(NB);
+    s.PADL = s.TP + 8;
+    s.Hs = base;          base += (NB + 3) & ~3;
+    s.ct = base;          base += (M + 3) & ~3;
+    s.rr = base;          base += (M / 2 + 1 + 3) & ~3;
+    s.hc = base;          base += s.TP;
+    s.ha = base;          base += s.TP;
+    s.u = base;
+    return s;
+}
+
+// Builds ct, rr, hc, ha from Hs (all in shared memory). Ends with a __syncthreads().
+__device__ __forceinline__ void build_taps(const NoiseSmem& s, int NB) {
+    const int M = 2 * (NB - 1), half = M / 2;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const float invM = 1.0f / (float)M;
+    for (int i = tid; i < M; i += nt) s.ct[i] = cospif(2.0f * (float)i * invM);
+    __syncthreads();
+    // r[j] = (1/M) (H_0 + (-1)^j H_{NB-1} + 2 sum_{m=1}^{NB-2} H_m cos(2 pi m j / M))        (irfft, :8-10)
+    for (int j = tid; j <= half; j += nt) {
+        float acc = 0.f;
+        int idx = j % M;
+        for (int m = 1; m < NB - 1; ++m) {
+            acc = fmaf(s.Hs[m], s.ct[idx], acc);
+            idx += j;
+            if (idx >= M) idx -= M;
+        }
+        const float edge = s.Hs[0] + ((j & 1) ? -s.Hs[NB - 1] : s.Hs[NB - 1]);
+        s.rr[j] = (2.f * acc + edge) * invM;
+    }
+    __syncthreads();
+    for (int q = tid; q < s.TP; q += nt) {
+        float c = 0.f, a = 0.f;
+        if (q < half) {
+            c = s.rr[q] * (0.5f + 0.5f * s.ct[q]);                 // r[q]     * hann[M/2+q]
+            a = s.rr[half - q] * (0.5f - 0.5f * s.ct[q]);          // r[M/2+q] * hann[q]
+        }
+        s.hc[q] = c;
+        s.ha[q] = a;
+    }
+    __syncthreads();
+}
+
+// Loads (or generates) the frame's noise into s.u[PADL .. PADL+hop) and zeroes the left pad.
+__device__ __forceinline__ void load_noise(const NoiseSmem& s, const float* __restrict__ noise_frame, int hop, uint32_t t,
+                                           uint32_t voice, uint32_t offset, uint2 key) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < s.PADL; i += nt) s.u[i] = 0.f;
+    float* u = s.u + s.PADL;
+    if (noise_frame) {
+        for (int i = tid; i < hop; i += nt) u[i] = noise_frame[i];
+    } else {
+        const int quads = (hop + 3) >> 2;
+        for (int q = tid; q < quads; q += nt) {
+            const float4 v = philox_noise4((uint32_t)q, t, voice, offset, key);
+            const int i = 4 * q;
+            if (i + 3 < hop) {
+                *reinterpret_cast<float4*>(u + i) = v;            // PADL and i are multiples of 4
+            } else {
+                if (i < hop) u[i] = v.x;
+                if (i + 1 < hop) u[i + 1] = v.y;
+                if (i + 2 < hop) u[i + 2] = v.z;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward: grid (T, B), hop/8 threads (hop % 8 == 0), thread owns outputs j0..j0+7
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) noise_fwd_kernel(const float* __restrict__ H, const float* __restrict__ noise,
+                                                        float* __restrict__ y, int accumulate, uint2 key, uint32_t offset,
+                                                        uint32_t voice_offset, int T, int NB, int hop) {
+    extern __shared__ __align__(16) float smem[];
+    const NoiseSmem s = carve_noise_smem(smem, NB, hop);
+    const int t = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const size_t frame = (size_t)b * T + t;
+    for (int m = tid; m < NB; m += blockDim.x) s.Hs[m] = H[frame * NB + m];
+    load_noise(s, noise ? noise + frame * hop : nullptr, hop, (uint32_t)t, voice_offset + (uint32_t)b, offset, key);
+    __syncthreads();
+    build_taps(s, NB);
+
+    const int half = NB - 1;
+    const int j0 = 8 * tid;
+    const float* u = s.u + s.PADL;
+    float acc[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) acc[r] = 0.f;
+    float win[16];
+    {
+        const float4 a = *reinterpret_cast<const float4*>(u + j0), c = *reinterpret_cast<const float4*>(u + j0 + 4);
+        win[8] = a.x; win[9] = a.y; win[10] = a.z; win[11] = a.w;
+        win[12] = c.x; win[13] = c.y; win[14] = c.z; win[15] = c.w;
+    }
+    const int qend = min(s.TP, j0 + 8);                 // lags beyond the frame start only see zeros
+    for (int q0 = 0; q0 < qend; q0 += 8) {
+        {
+            const float4 a = *reinterpret_cast<const float4*>(u + j0 - q0 - 8);
+            const float4 c = *reinterpret_cast<const float4*>(u + j0 - q0 - 4);
+            win[0] = a.x; win[1] = a.y; win[2] = a.z; win[3] = a.w;
+            win[4] = c.x; win[5] = c.y; win[6] = c.z; win[7] = c.w;
+        }
+        const float4 ta = *reinterpret_cast<const float4*>(s.hc + q0), tb = *reinterpret_cast<const float4*>(s.hc + q0 + 4);
+        const float tap[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
+#pragma unroll
+        for (int d = 0; d < 8; ++d)
+#pragma unroll
+            for (int r = 0; r < 8; ++r) acc[r] = fmaf(tap[d], win[8 + r - d], acc[r]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) win[8 + i] = win[i];
+    }
+    // wrapped taps: lag hop-half+i only reaches outputs j >= hop-half            (the roll by -M/2, :20)
+    const int jw = hop - half;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const int jp = j0 + r - jw;
+        if (jp >= 0) {
+            float a2 = 0.f;
+            for (int i = 0; i <= jp; ++i) a2 = fmaf(s.ha[i], u[jp - i], a2);
+            acc[r] += a2;
+        }
+    }
+    float* yp = y + frame * hop + j0;
+    float4 o0 = make_float4(acc[0], acc[1], acc[2], acc[3]), o1 = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    if (accumulate) {
+        const float4 p0 = *reinterpret_cast<const float4*>(yp), p1 = *reinterpret_cast<const float4*>(yp + 4);
+        o0.x += p0.x; o0.y += p0.y; o0.z += p0.z; o0.w += p0.w;
+        o1.x += p1.x; o1.y += p1.y; o1.z += p1.z; o1.w += p1.w;
+    }
+    *reinterpret_cast<float4*>(yp) = o0;
+    *reinterpret_cast<float4*>(yp + 4) = o1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward: grid (T, B), (TP/8)*nsl threads.  Thread (qg, sl) owns taps 8qg..8qg+7 and the sl-th slice
+// of the frame's samples:   d hc[q] = sum_j g[j] u[j-q]        d ha[i] = sum_{j'<M/2} g[hop-M/2+j'] u[j'-i]
+// then   d r[p] = d hc[p] hann[M/2+p] + d ha[M/2-p] hann[M/2-p]      (p = 0..M/2)
+//        d H[m] = (kappa_m / M) sum_p d r[p] cos(2 pi m p / M),  kappa = 1 at the two edge bands, else 2.
+// The gradient does not depend on H itself (the filter is linear in H).
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ inline int noise_bwd_slices(int NB, int hop) {
+    const int groups = noise_tp(NB) / 8;
+    int nsl = 1;
+    while (nsl * 2 * groups <= 128 && hop % (16 * nsl) == 0) nsl *= 2;
+    return nsl;
+}
+
+__host__ __device__ inline size_t noise_bwd_smem_floats(int NB, int hop) {
+    const int M = 2 * (NB - 1), TP = noise_tp(NB), nsl = noise_bwd_slices(NB, hop);
+    return ((M + 3) & ~3) + ((M / 2 + 1 + 3) & ~3) + (size_t)hop + (TP + 8) + (TP + 8 + hop) + 2 * (size_t)TP * nsl;
+}
+
+__global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict__ g, const float* __restrict__ noise,
+                                                        float* __restrict__ gH, uint2 key, uint32_t offset,
+                                                        uint32_t voice_offset, int T, int NB, int hop, int nsl) {
+    extern __shared__ __align__(16) float smem[];
+    const int M = 2 * (NB - 1), half = NB - 1, TP = noise_tp(NB), PADL = TP + 8;
+    float* ct = smem;
+    float* dr = ct + ((M + 3) & ~3);
+    float* gs = dr + ((half + 1 + 3) & ~3);            // [hop]    upstream gradient of this frame
+    float* g2 = gs + hop;                              // [TP+8]   gradient seen by the wrapped taps, zero padded
+    NoiseSmem s;
+    s.TP = TP; s.PADL = PADL;
+    s.u = g2 + TP + 8;                                 // [PADL+hop]
+    float* dpc = s.u + PADL + hop;                     // [TP][nsl] partial d hc
+    float* dpa = dpc + (size_t)TP * nsl;               // [TP][nsl] partial d ha
+    const int t = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
+    const size_t frame = (size_t)b * T + t;
+    const int jw = hop - half;
+    const float invM = 1.0f / (float)M;
+
+    for (int i = tid; i < M; i += nt) ct[i] = cospif(2.0f * (float)i * invM);
+    for (int i = tid; i < hop; i += nt) gs[i] = g[frame * hop + i];
+    for (int i = tid; i < TP + 8; i += nt) g2[i] = (i < half) ? g[frame * hop + jw + i] : 0.f;
+    load_noise(s, noise ? noise + frame * hop : nullptr, hop, (uint32_t)t, voice_offset + (uint32_t)b, offset, key);
+    __syncthreads();
+
+    const float* u = s.u + PADL;
+    const int qg = tid / nsl, sl = tid % nsl;
+    const int q0 = 8 * qg, SL = hop / nsl;
+    float acc[8], acc2[8];
+#pragma unroll
+    for (int d = 0; d < 8; ++d) acc[d] = acc2[d] = 0.f;
+    {
+        const int jb0 = sl * SL, jend = jb0 + SL;
+        int jb = max(jb0, q0);
+        float win[16];
+        if (jb < jend) {
+            const float4 a = *reinterpret_cast<const float4*>(u + jb - q0 - 8), c = *reinterpret_cast<const float4*>(u + jb - q0 - 4);
+            win[8] = a.x; win[9] = a.y; win[10] = a.z; win[11] = a.w;
+            win[12] = c.x; win[13] = c.y; win[14] = c.z; win[15] = c.w;
+        }
+        for (; jb < jend; jb += 8) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) win[i] = win[8 + i];
+            const float4 a = *reinterpret_cast<const float4*>(u + jb - q0), c = *reinterpret_cast<const float4*>(u + jb - q0 + 4);
+            win[8] = a.x; win[9] = a.y; win[10] = a.z; win[11] = a.w;
+            win[12] = c.x; win[13] = c.y; win[14] = c.z; win[15] = c.w;
+            const float4 ga = *reinterpret_cast<const float4*>(gs + jb), gb = *reinterpret_cast<const float4*>(gs + jb + 4);
+            const float gv[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int d = 0; d < 8; ++d) acc[d] = fmaf(gv[r], win[8 + r - d], acc[d]);
+        }
+        // wrapped taps: blocks of j' dealt round-robin to the slices
+        for (int jp = 8 * sl; jp < TP; jp += 8 * nsl) {
+            if (jp < q0) continue;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) win[i] = u[jp - q0 - 8 + i];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const float gr = g2[jp + r];
+#pragma unroll
+                for (int d = 0; d < 8; ++d) acc2[d] = fmaf(gr, win[8 + r - d], acc2[d]);
+            }
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < 8; ++d) {
+        dpc[(size_t)(q0 + d) * nsl + sl] = acc[d];
+        dpa[(size_t)(q0 + d) * nsl + sl] = acc2[d];
+    }
+    __syncthreads();
+    for (int p = tid; p <= half; p += nt) {
+        float v = 0.f;
+        if (p < half) {
+            float sc = 0.f;
+            for (int i = 0; i < nsl; ++i) sc += dpc[(size_t)p * nsl + i];
+            v = sc * (0.5f + 0.5f * ct[p]);
+        }
+        if (p >= 1) {
+            const int i0 = half - p;
+            float sa = 0.f;
+            for (int i = 0; i < nsl; ++i) sa += dpa[(size_t)i0 * nsl + i];
+            v = fmaf(sa, 0.5f - 0.5f * ct[i0], v);
+        }
+        dr[p] = v;
+    }
+    __syncthreads();
+    for (int m = tid; m < NB; m += nt) {
+        float a2 = 0.f;
+        int idx = 0;
+        for (int p = 0; p <= half; ++p) {
+            a2 = fmaf(dr[p], ct[idx], a2);
+            idx += m;
+            if (idx >= M) idx -= M;
+        }
+        gH[frame * NB + m] = a2 * ((m == 0 || m == NB - 1) ? invM : 2.f * invM);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// small utility kernels
+// ------------------------------------------------------------------------------------------------
+__global__ void noise_uniform_kernel(float* __restrict__ out, uint2 key, uint32_t offset, uint32_t voice_offset, int T,
+                                     int hop, long long total_quads) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total_quads) return;
+    const int qpf = (hop + 3) >> 2;
+    const long long frame = i / qpf;
+    const int q = (int)(i % qpf);
+    const uint32_t b = (uint32_t)(frame / T), t = (uint32_t)(frame % T);
+    const float4 v = philox_noise4((uint32_t)q, t, voice_offset + b, offset, key);
+    float* o = out + frame * hop + 4 * q;
+    const float vals[4] = {v.x, v.y, v.z, v.w};
+    for (int e = 0; e < 4; ++e)
+        if (4 * q + e < hop) o[e] = vals[e];
+}
+
+// amp_to_impulse_response (:7-22) on its own: one CTA per row
+__global__ void __launch_bounds__(256) amp_to_ir_kernel(const float* __restrict__ H, float* __restrict__ ir, int NB, int target) {
+    extern __shared__ __align__(16) float smem[];
+    const NoiseSmem s = carve_noise_smem(smem, NB, 0);
+    const size_t row = blockIdx.x;
+    const int half = NB - 1;
+    for (int m = threadIdx.x; m < NB; m += blockDim.x) s.Hs[m] = H[row * NB + m];
+    __syncthreads();
+    build_taps(s, NB);
+    float* o = ir + row * target;
+    for (int i = threadIdx.x; i < target; i += blockDim.x) {
+        float v = 0.f;
+        if (i < half) v = s.hc[i];
+        const int w = i - (target - half);
+        if (w >= 0) v += s.ha[w];                        // M == target: both parts land on the same taps? no: ranges are disjoint
+        o[i] = v;
+    }
+}
+
+static int check_noise_shape(const char* fn, int B, int T, int NB, int hop) {
+    DDSP_REQUIRE(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
+    DDSP_REQUIRE(T >= 1, "%s: T=%d must be >= 1", fn, T);
+    DDSP_REQUIRE(NB >= 2, "%s: NB=%d must be >= 2", fn, NB);
+    DDSP_REQUIRE(hop >= 8 && hop % 8 == 0 && hop <= 4096, "%s: hop=%d must be a multiple of 8 in [8,4096]", fn, hop);
+    DDSP_REQUIRE(2 * (NB - 1) <= hop, "%s: FIR length 2(NB-1)=%d exceeds hop=%d (filtered_noise.py:19 pads by hop-M)", fn,
+                 2 * (NB - 1), hop);
+    return 0;
+}
+
+template <typename Kern>
+static int reserve_smem(Kern kern, size_t bytes, const char* name) {
+    DDSP_REQUIRE(bytes <= 227 * 1024, "%s: needs %zu B of shared memory (> 227 KB)", name, bytes);
+    if (bytes > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        DDSP_REQUIRE(e == cudaSuccess, "%s: cannot reserve %zu B of shared memory: %s", name, bytes, cudaGetErrorString(e));
+    }
+    return 0;
+}
+
+}  // namespace ddsp
+
+using namespace ddsp;
+
+extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, int accumulate, uint64_t seed,
+                                  uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop, void* stream) {
+    if (check_noise_shape("ddsp_noise_forward", B, T, NB, hop)) return 1;
+    DDSP_REQUIRE(H && y, "ddsp_noise_forward: null pointer argument");
+    const size_t smem = sizeof(float) * noise_smem_floats(NB, hop);
+    if (reserve_smem(noise_fwd_kernel, smem, "noise_fwd_kernel")) return 1;
+    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
+    noise_fwd_kernel<<<dim3(T, B), hop / 8, smem, static_cast<cudaStream_t>(stream)>>>(H, noise, y, accumulate, key, offset,
+                                                                                      voice_offset, T, NB, hop);
+    DDSP_CHECK_LAUNCH("noise_fwd_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH, uint64_t seed, uint32_t offset,
+                                   uint32_t voice_offset, int B, int T, int NB, int hop, void* stream) {
+    if (check_noise_shape("ddsp_noise_backward", B, T, NB, hop)) return 1;
+    DDSP_REQUIRE(g && gH, "ddsp_noise_backward: null pointer argument");
+    const int nsl = noise_bwd_slices(NB, hop);
+    const int threads = noise_tp(NB) / 8 * nsl;
+    DDSP_REQUIRE(threads <= 512, "ddsp_noise_backward: NB=%d needs %d threads per frame (max 512)", NB, threads);
+    const size_t smem = sizeof(float) * noise_bwd_smem_floats(NB, hop);
+    if (reserve_smem(noise_bwd_kernel, smem, "noise_bwd_kernel")) return 1;
+    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
+    noise_bwd_kernel<<<dim3(T, B), threads, smem, static_cast<cudaStream_t>(stream)>>>(g, noise, gH, key, offset, voice_offset,
+                                                                                      T, NB, hop, nsl);
+    DDSP_CHECK_LAUNCH("noise_bwd_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_noise_uniform(float* out, uint64_t seed, uint32_t offset, uint32_t voice_offset, int B, int T, int hop,
+                                  void* stream) {
+    DDSP_REQUIRE(out && B >= 1 && T >= 1 && hop >= 1, "ddsp_noise_uniform: bad arguments");
+    const long long quads = (long long)B * T * ((hop + 3) >> 2);
+    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
+    noise_uniform_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        out, key, offset, voice_offset, T, hop, quads);
+    DDSP_CHECK_LAUNCH("noise_uniform_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_amp_to_impulse_response(const float* H, float* ir, int R, int NB, int target, void* stream) {
+    DDSP_REQUIRE(H && ir && R >= 1 && NB >= 2, "ddsp_amp_to_impulse_response: bad arguments");
+    DDSP_REQUIRE(2 * (NB - 1) <= target, "ddsp_amp_to_impulse_response: FIR length %d exceeds target %d", 2 * (NB - 1), target);
+    const size_t smem = sizeof(float) * noise_smem_floats(NB, 0);
+    if (reserve_smem(amp_to_ir_kernel, smem, "amp_to_ir_kernel")) return 1;
+    amp_to_ir_kernel<<<R, 256, smem, static_cast<cudaStream_t>(stream)>>>(H, ir, NB, target);
+    DDSP_CHECK_LAUNCH("amp_to_ir_kernel");
+    return 0;
+}

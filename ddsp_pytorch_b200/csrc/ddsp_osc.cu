@@ -1,0 +1,479 @@
+// Harmonic oscillator bank for sm_100a -- replaces OscillatorBank (harmonic_oscillator.py:24-62).
+//
+// The reference materialises ~10 tensors of shape [B,N,K] (upsampled rad/sample, cumsum, sin, ...).
+// Here nothing of that shape ever exists:
+//   osc_prepare_kernel   frame rate: Nyquist mask + normalisation of c (:31-33), active-harmonic
+//                        count, and an fp64 scan of the fundamental's phase over FRAMES (the
+//                        cumsum over samples, :41, has a closed form inside each hop).
+//   osc_synth_kernel     one CTA per (voice, hop segment): per sample one fp64 phase -> (sin, delta)
+//                        seed, then all harmonics by the Reinsch sine recurrence in registers
+//                        (2 FP32 ops per harmonic-sample, no MUFU), two FFMA dot products with the
+//                        segment's amplitude pair held in shared memory, float4 store.
+//   osc_grad_kernel      same recurrence, accumulates g*a_up*sin and g*a_up*w*sin per harmonic,
+//                        reduced over the segment's samples through shared memory.
+//   osc_finalize_kernel  frame rate: gathers the two segments touching each frame and runs the
+//                        backward of mask+normalise.
+// Harmonics masked in both frames of a segment have zero amplitude for the whole segment and are
+// skipped (the loop runs to the segment's active count), exactly as multiplying by zero would.
+#include "ddsp_common.cuh"
+
+namespace ddsp {
+
+// ------------------------------------------------------------------------------------------------
+// frame-rate preparation: one CTA per voice
+// ------------------------------------------------------------------------------------------------
+constexpr int PREP_THREADS = 256;
+
+__global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
+    const float* __restrict__ f0, const float* __restrict__ c, float* __restrict__ cn, float* __restrict__ csum,
+    int* __restrict__ kact, double* __restrict__ phase0, int T, int K, int hop, int sample_rate) {
+    const int b = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = PREP_THREADS / 32;
+    __shared__ double warp_tot[NW];
+    __shared__ double carry_s;
+
+    // ---- phase prefix over segments, fp64, in cycles -------------------------------------------
+    // E_0 = -(hop/2) u_0 ; E_{s+1} = E_s + hop*(u_{max(s-1,0)} + u_s)/2          (u = f0 / sample_rate)
+    const float* f0b = f0 + (size_t)b * T;
+    double* Eb = phase0 + (size_t)b * (T + 1);
+    const double inv_sr = 1.0 / (double)sample_rate;
+    if (tid == 0) {
+        const double e0 = -0.5 * hop * ((double)f0b[0] * inv_sr);
+        carry_s = e0;
+        Eb[0] = e0 - floor(e0);
+    }
+    __syncthreads();
+    for (int base = 0; base < T; base += PREP_THREADS) {
+        const int s = base + tid;
+        double v = 0.0;
+        if (s < T) {
+            const double uL = (double)f0b[s > 0 ? s - 1 : 0] * inv_sr;
+            const double uR = (double)f0b[s] * inv_sr;
+            v = 0.5 * hop * (uL + uR);
+        }
+        // inclusive scan inside the warp, then across warps
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double n = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += n;
+        }
+        if (lane == 31) warp_tot[warp] = v;
+        __syncthreads();
+        double pre = carry_s;
+        for (int w = 0; w < warp; ++w) pre += warp_tot[w];
+        const double e = pre + v;                       // E_{s+1}
+        if (s < T) Eb[s + 1] = e - floor(e);
+        __syncthreads();
+        if (tid == PREP_THREADS - 1) carry_s = e - floor(e);   // keep the carry small: only the fraction matters
+        __syncthreads();
+    }
+
+    // ---- mask + normalise each frame: one warp per frame ---------------------------------------
+    const float nyq = (float)(sample_rate / 2);        // integer floor, compared as float (:31)
+    for (int t = warp; t < T; t += NW) {
+        const float f = f0b[t];
+        const float* cr = c + ((size_t)b * T + t) * K;
+        float* cnr = cn + ((size_t)b * T + t) * K;
+        float sum = 0.f;
+        int last = 0;
+        for (int k = lane; k < K; k += 32) {
+            const bool masked = (float)(k + 1) * f > nyq;
+            const float v = masked ? 0.f : cr[k];
+            sum += v;
+            if (!masked) last = k + 1;
+        }
+        sum = warp_sum(sum);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+        if (!(sum > 0.f)) last = K;                     // 0/0 or NaN frame: keep every harmonic so NaN propagates like :33
+        for (int k = lane; k < K; k += 32) {
+            const bool masked = (float)(k + 1) * f > nyq;
+            cnr[k] = (masked ? 0.f : cr[k]) / sum;
+        }
+        if (lane == 0) {
+            csum[(size_t)b * T + t] = sum;
+            kact[(size_t)b * T + t] = last;
+        }
+    }
+}
+
+// Everything a thread needs about its segment.
+struct Segment {
+    int tL, tR;        // frames interpolated
+    int r_lo, r_hi;    // valid sample range inside the segment
+    long long n0;      // global sample index of r = 0 (may be negative for s = 0)
+    double E, uL, du;  // phase prefix, left increment, (uR-uL)/(2*hop)    [cycles]
+};
+
+__device__ __forceinline__ Segment make_segment(int s, int T, int hop, const float* __restrict__ f0b,
+                                                const double* __restrict__ Eb, double inv_sr) {
+    Segment g;
+    g.tL = s > 0 ? s - 1 : 0;
+    g.tR = s < T ? s : T - 1;
+    g.r_lo = s == 0 ? hop / 2 : 0;
+    g.r_hi = s == T ? hop / 2 : hop;
+    g.n0 = (long long)s * hop - hop / 2;
+    g.E = Eb[s];
+    g.uL = (double)f0b[g.tL] * inv_sr;
+    g.du = ((double)f0b[g.tR] * inv_sr - g.uL) / (2.0 * hop);
+    return g;
+}
+
+__device__ __forceinline__ PhaseSeed seed_at(const Segment& g, int r) {
+    const double rr = (double)(r + 1);
+    return phase_seed(wrap_cycles(fma(g.du * rr, rr, fma(rr, g.uL, g.E))));
+}
+
+// ------------------------------------------------------------------------------------------------
+// synthesis: grid (T+1, B), hop/R threads, R consecutive samples per thread
+// ------------------------------------------------------------------------------------------------
+template <int R>
+__global__ void __launch_bounds__(512) osc_synth_kernel(
+    const float* __restrict__ cn, const float* __restrict__ a, const float* __restrict__ f0,
+    const int* __restrict__ kact, const double* __restrict__ phase0, float* __restrict__ y,
+    float* __restrict__ z_save, int accumulate, int T, int K, int hop, double inv_sr) {
+    extern __shared__ __align__(16) float2 amp[];      // (c'_L[k], c'_R[k]-c'_L[k]) for the active harmonics
+    const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const Segment g = make_segment(s, T, hop, f0 + (size_t)b * T, phase0 + (size_t)b * (T + 1), inv_sr);
+
+    const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
+    const int kmax = max(kact[fL], kact[fR]);
+    const int kpad = (kmax + 1) & ~1;
+    {
+        const float* cl = cn + fL * K;
+        const float* cr = cn + fR * K;
+        for (int k = tid; k < kpad; k += blockDim.x) {
+            float2 v = make_float2(0.f, 0.f);
+            if (k < kmax) {
+                const float l = cl[k];
+                v = make_float2(l, cr[k] - l);
+            }
+            amp[k] = v;
+        }
+    }
+    __syncthreads();
+
+    const int r0 = tid * R;
+    if (r0 >= g.r_hi || r0 + R <= g.r_lo) return;      // the half-filled first / last segment
+
+    float sn[R], dn[R], dl[R], Pe[R], Po[R], Qe[R], Qo[R];
+    float sg[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+        const PhaseSeed p = seed_at(g, r0 + j);
+        sn[j] = p.sin1;
+        dn[j] = p.sin1;                                // d_1 = s_1 - s_0, s_0 = 0
+        dl[j] = p.delta;
+        sg[j] = p.sigma;
+        Pe[j] = Po[j] = Qe[j] = Qo[j] = 0.f;
+    }
+
+    // Reinsch recurrence over harmonics m = 1..kmax:  d_{m+1} = d_m + delta*s_m ; s_{m+1} = s_m + d_{m+1}
+    const float4* amp4 = reinterpret_cast<const float4*>(amp);
+#pragma unroll 2
+    for (int k = 0; k < kpad; k += 2) {
+        const float4 A = amp4[k >> 1];                 // odd harmonic (x,y), even harmonic (z,w)
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            Po[j] = fmaf(A.x, sn[j], Po[j]);
+            Qo[j] = fmaf(A.y, sn[j], Qo[j]);
+            dn[j] = fmaf(dl[j], sn[j], dn[j]);
+            sn[j] += dn[j];
+        }
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            Pe[j] = fmaf(A.z, sn[j], Pe[j]);
+            Qe[j] = fmaf(A.w, sn[j], Qe[j]);
+            dn[j] = fmaf(dl[j], sn[j], dn[j]);
+            sn[j] += dn[j];
+        }
+    }
+
+    const float aL = a[fL], da = a[fR] - aL;
+    const float inv_hop = 1.0f / (float)hop;
+    float out[R], zs[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+        const float w = ((float)(r0 + j) + 0.5f) * inv_hop;
+        const float zP = fmaf(sg[j], Po[j], Pe[j]);    // sin(m theta) = sigma^m sin(m theta')
+        const float zQ = fmaf(sg[j], Qo[j], Qe[j]);
+        zs[j] = fmaf(w, zQ, zP);
+        out[j] = fmaf(w, da, aL) * zs[j];
+    }
+    const size_t N = (size_t)T * hop;
+    float* yp = y + (size_t)b * N + (g.n0 + r0);
+    float* zp = z_save ? z_save + (size_t)b * N + (g.n0 + r0) : nullptr;
+    if (R == 4 && ((hop & 7) == 0)) {
+        float4 o = make_float4(out[0], out[1], out[2], out[3]);
+        if (accumulate) {
+            const float4 p = *reinterpret_cast<const float4*>(yp);
+            o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+        }
+        *reinterpret_cast<float4*>(yp) = o;
+        if (zp) *reinterpret_cast<float4*>(zp) = make_float4(zs[0], zs[1], zs[2], zs[3]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            yp[j] = accumulate ? yp[j] + out[j] : out[j];
+            if (zp) zp[j] = zs[j];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward over samples: grid (T+1, B), hop/R threads.
+//   G0[b,s,k] = sum_r g*a_up*sin(k theta),  G1[b,s,k] = sum_r g*a_up*w*sin(k theta)     (segment s)
+//   A0[b,s]   = sum_r g*z,                  A1[b,s]   = sum_r g*z*w
+// Harmonics are processed in chunks of CH; every thread parks its R-sample partial sums in shared
+// memory ([CH][NT] float2, rows padded by 4 floats so the float4 row sweeps are conflict-free) and
+// one thread per harmonic sums its row.
+// ------------------------------------------------------------------------------------------------
+constexpr int GRAD_CH = 32;
+
+template <int R>
+__global__ void __launch_bounds__(512) osc_grad_kernel(
+    const float* __restrict__ gup, const float* __restrict__ a, const float* __restrict__ f0,
+    const float* __restrict__ z_save, const int* __restrict__ kact, const double* __restrict__ phase0,
+    float2* __restrict__ gseg, float2* __restrict__ gaseg, int T, int K, int hop, double inv_sr) {
+    extern __shared__ __align__(16) float part[];      // [GRAD_CH][2*NT + 4]
+    __shared__ float red[2][16];
+    const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, NT = blockDim.x;
+    const int stride = 2 * NT + 4;
+    const Segment g = make_segment(s, T, hop, f0 + (size_t)b * T, phase0 + (size_t)b * (T + 1), inv_sr);
+    const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
+    const int kmax = max(kact[fL], kact[fR]);
+
+    const int r0 = tid * R;
+    const bool live = !(r0 >= g.r_hi || r0 + R <= g.r_lo);
+    float sn[R], dn[R], dl[R], ug[R], uw[R], ugo[R], uwo[R];
+    float ga0 = 0.f, ga1 = 0.f;
+    if (live) {
+        const float aL = a[fL], da = a[fR] - aL;
+        const float inv_hop = 1.0f / (float)hop;
+        const size_t N = (size_t)T * hop;
+        const float* gp = gup + (size_t)b * N + (g.n0 + r0);
+        const float* zp = z_save + (size_t)b * N + (g.n0 + r0);
+#pragma unroll
+        for (int j = 0; j < R; ++j) {
+            const PhaseSeed p = seed_at(g, r0 + j);
+            sn[j] = p.sin1;
+            dn[j] = p.sin1;
+            dl[j] = p.delta;
+            const float w = ((float)(r0 + j) + 0.5f) * inv_hop;
+            const float gj = gp[j];
+            const float gz = gj * zp[j];
+            ga0 += gz;
+            ga1 = fmaf(gz, w, ga1);
+            ug[j] = gj * fmaf(w, da, aL);
+            uw[j] = ug[j] * w;
+            ugo[j] = ug[j] * p.sigma;
+            uwo[j] = uw[j] * p.sigma;
+        }
+    }
+
+    float2* gout = gseg + ((size_t)b * (T + 1) + s) * K;
+    for (int k0 = 0; k0 < kmax; k0 += GRAD_CH) {
+        const int kn = min(GRAD_CH, kmax - k0);
+        const int kn2 = (kn + 1) & ~1;
+        if (live) {
+            for (int kk = 0; kk < kn2; kk += 2) {
+                float p0o = 0.f, p1o = 0.f, p0e = 0.f, p1e = 0.f;
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    p0o = fmaf(ugo[j], sn[j], p0o);
+                    p1o = fmaf(uwo[j], sn[j], p1o);
+                    dn[j] = fmaf(dl[j], sn[j], dn[j]);
+                    sn[j] += dn[j];
+                }
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    p0e = fmaf(ug[j], sn[j], p0e);
+                    p1e = fmaf(uw[j], sn[j], p1e);
+                    dn[j] = fmaf(dl[j], sn[j], dn[j]);
+                    sn[j] += dn[j];
+                }
+                *reinterpret_cast<float2*>(&part[kk * stride + 2 * tid]) = make_float2(p0o, p1o);
+                *reinterpret_cast<float2*>(&part[(kk + 1) * stride + 2 * tid]) = make_float2(p0e, p1e);
+            }
+        } else {
+            for (int kk = 0; kk < kn2; ++kk)
+                *reinterpret_cast<float2*>(&part[kk * stride + 2 * tid]) = make_float2(0.f, 0.f);
+        }
+        __syncthreads();
+        for (int row = tid; row < kn; row += NT) {
+            const float4* p4 = reinterpret_cast<const float4*>(&part[row * stride]);
+            float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
+            for (int c4 = 0; c4 < NT / 2; ++c4) {
+                const float4 v = p4[c4];
+                s0 += v.x; s1 += v.y; t0 += v.z; t1 += v.w;
+            }
+            if (NT & 1) {                                   // odd thread count (tiny hops): last column
+                s0 += part[row * stride + 2 * (NT - 1)];
+                s1 += part[row * stride + 2 * (NT - 1) + 1];
+            }
+            gout[k0 + row] = make_float2(s0 + t0, s1 + t1);
+        }
+        __syncthreads();
+    }
+
+    // loudness partials: block reduction
+    ga0 = warp_sum(ga0);
+    ga1 = warp_sum(ga1);
+    if ((tid & 31) == 0) { red[0][tid >> 5] = ga0; red[1][tid >> 5] = ga1; }
+    __syncthreads();
+    if (tid == 0) {
+        float x0 = 0.f, x1 = 0.f;
+        for (int w = 0; w < (NT + 31) / 32; ++w) { x0 += red[0][w]; x1 += red[1][w]; }
+        gaseg[(size_t)b * (T + 1) + s] = make_float2(x0, x1);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// frame-rate backward: one warp per frame. Frame t is the LEFT frame of segment t+1 (and of segment 0
+// when t = 0) with weight 1-w, and the RIGHT frame of segment t (and of segment T when t = T-1) with
+// weight w.  Then the backward of c' = m*c / sum(m*c)   (harmonic_oscillator.py:32-33).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) osc_finalize_kernel(
+    const float2* __restrict__ gseg, const float2* __restrict__ gaseg, const float* __restrict__ cn,
+    const float* __restrict__ csum, const int* __restrict__ kact, const float* __restrict__ f0,
+    float* __restrict__ gc, float* __restrict__ ga, int B, int T, int K, int sample_rate) {
+    const int lane = threadIdx.x & 31;
+    const long long frame = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (frame >= (long long)B * T) return;
+    const int b = (int)(frame / T), t = (int)(frame % T);
+    const float2* segR = gseg + ((size_t)b * (T + 1) + t) * K;        // segment t   : frame t is RIGHT
+    const float2* segL = segR + K;                                     // segment t+1 : frame t is LEFT
+    const float2* seg0 = gseg + ((size_t)b * (T + 1)) * K;            // segment 0   : frame 0 is also LEFT
+    const float2* segT = gseg + ((size_t)b * (T + 1) + T) * K;        // segment T   : frame T-1 is also RIGHT
+    const int kt = kact[frame];
+    const float S = csum[frame];
+    const float f = f0[frame];
+    const float nyq = (float)(sample_rate / 2);
+    const float* cnr = cn + (size_t)frame * K;
+    float* gcr = gc + (size_t)frame * K;
+
+    auto grad_cn = [&](int k) {
+        const float2 l = segL[k], r = segR[k];
+        float v = (l.x - l.y) + r.y;
+        if (t == 0) { const float2 e = seg0[k]; v += e.x - e.y; }
+        if (t == T - 1) { const float2 e = segT[k]; v += e.y; }
+        return v;
+    };
+    float dot = 0.f;
+    for (int k = lane; k < kt; k += 32) dot = fmaf(grad_cn(k), cnr[k], dot);
+    dot = warp_sum(dot);
+    for (int k = lane; k < K; k += 32) {
+        float v = 0.f;
+        if (k < kt && !((float)(k + 1) * f > nyq)) v = (grad_cn(k) - dot) / S;
+        gcr[k] = v;
+    }
+    if (lane == 0) {
+        const float2* ab = gaseg + (size_t)b * (T + 1);
+        float v = (ab[t + 1].x - ab[t + 1].y) + ab[t].y;
+        if (t == 0) v += ab[0].x - ab[0].y;
+        if (t == T - 1) v += ab[T].y;
+        ga[frame] = v;
+    }
+}
+
+// pick samples-per-thread: hop must split into an even number of threads of R samples, at most 512 threads
+static int pick_R(int hop, int prefer) {
+    for (int R = prefer; R >= 1; R >>= 1)
+        if (hop % (2 * R) == 0 && hop / R <= 512 && (hop / R >= 32 || R == 1)) return R;
+    for (int R = prefer; R >= 1; R >>= 1)
+        if (hop % (2 * R) == 0 && hop / R <= 512) return R;
+    return 0;
+}
+
+static int check_osc_shape(const char* fn, int B, int T, int K, int hop, int sample_rate) {
+    DDSP_REQUIRE(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
+    DDSP_REQUIRE(T >= 1, "%s: T=%d must be >= 1", fn, T);
+    DDSP_REQUIRE(K >= 1 && K <= 4096, "%s: K=%d out of range [1,4096]", fn, K);
+    DDSP_REQUIRE(hop >= 2 && (hop % 2) == 0, "%s: hop=%d must be even and >= 2", fn, hop);
+    DDSP_REQUIRE(sample_rate >= 1, "%s: sample_rate=%d must be positive", fn, sample_rate);
+    DDSP_REQUIRE(pick_R(hop, 8) > 0, "%s: hop=%d too large for one CTA per segment (max 4096)", fn, hop);
+    return 0;
+}
+
+}  // namespace ddsp
+
+using namespace ddsp;
+
+extern "C" size_t ddsp_osc_state_bytes(int B, int T, int K) {
+    if (B < 1 || T < 1 || K < 1) return 0;
+    return align_up(sizeof(double) * (size_t)B * (T + 1), 256) + align_up(sizeof(float) * (size_t)B * T * K, 256) +
+           align_up(sizeof(float) * (size_t)B * T, 256) + align_up(sizeof(int) * (size_t)B * T, 256);
+}
+
+extern "C" size_t ddsp_osc_backward_scratch_bytes(int B, int T, int K) {
+    if (B < 1 || T < 1 || K < 1) return 0;
+    return align_up(sizeof(float2) * (size_t)B * (T + 1) * K, 256) + align_up(sizeof(float2) * (size_t)B * (T + 1), 256);
+}
+
+extern "C" int ddsp_osc_forward(const float* f0, const float* c, const float* a, float* y, float* z_save, void* state,
+                                int accumulate, int B, int T, int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_forward", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(f0 && c && a && y && state, "ddsp_osc_forward: null pointer argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const OscState S = carve_osc_state(state, B, T, K);
+    osc_prepare_kernel<<<B, PREP_THREADS, 0, st>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, T, K, hop, sample_rate);
+    DDSP_CHECK_LAUNCH("osc_prepare_kernel");
+    const int R = pick_R(hop, 4);
+    const dim3 grid(T + 1, B);
+    const size_t smem = sizeof(float2) * ((K + 1) & ~1);
+    const double inv_sr = 1.0 / (double)sample_rate;
+#define LAUNCH_SYNTH(RR)                                                                                              \
+    osc_synth_kernel<RR><<<grid, hop / RR, smem, st>>>(S.cn, a, f0, S.kact, S.phase0, y, z_save, accumulate, T, K, hop, \
+                                                       inv_sr)
+    switch (R) {
+        case 4: LAUNCH_SYNTH(4); break;
+        case 2: LAUNCH_SYNTH(2); break;
+        default: LAUNCH_SYNTH(1); break;
+    }
+#undef LAUNCH_SYNTH
+    DDSP_CHECK_LAUNCH("osc_synth_kernel");
+    return 0;
+}
+
+template <int R>
+static int launch_grad(const float* g, const float* a, const float* f0, const float* z, const OscState& S, float2* gseg,
+                       float2* gaseg, int B, int T, int K, int hop, int sample_rate, cudaStream_t st) {
+    const int NT = hop / R;
+    const size_t smem = sizeof(float) * GRAD_CH * (2 * NT + 4);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(osc_grad_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        DDSP_REQUIRE(e == cudaSuccess, "osc_grad_kernel: cannot reserve %zu B of shared memory: %s", smem,
+                     cudaGetErrorString(e));
+    }
+    osc_grad_kernel<R><<<dim3(T + 1, B), NT, smem, st>>>(g, a, f0, z, S.kact, S.phase0, gseg, gaseg, T, K, hop,
+                                                        1.0 / (double)sample_rate);
+    DDSP_CHECK_LAUNCH("osc_grad_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_osc_backward(const float* g, const float* f0, const float* a, const float* z_save, const void* state,
+                                 void* scratch, float* gc, float* ga, int B, int T, int K, int hop, int sample_rate,
+                                 void* stream) {
+    if (check_osc_shape("ddsp_osc_backward", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(g && f0 && a && z_save && state && scratch && gc && ga, "ddsp_osc_backward: null pointer argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
+    float2* gseg = reinterpret_cast<float2*>(scratch);
+    float2* gaseg = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) +
+                                              align_up(sizeof(float2) * (size_t)B * (T + 1) * K, 256));
+    int rc;
+    switch (pick_R(hop, 8)) {
+        case 8: rc = launch_grad<8>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
+        case 4: rc = launch_grad<4>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
+        case 2: rc = launch_grad<2>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
+        default: rc = launch_grad<1>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
+    }
+    if (rc) return rc;
+    const long long frames = (long long)B * T;
+    const int wpb = 8;
+    osc_finalize_kernel<<<(unsigned)((frames + wpb - 1) / wpb), wpb * 32, 0, st>>>(gseg, gaseg, S.cn, S.csum, S.kact, f0, gc,
+                                                                                 ga, B, T, K, sample_rate);
+    DDSP_CHECK_LAUNCH("osc_finalize_kernel");
+    return 0;
+}

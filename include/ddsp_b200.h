@@ -1,0 +1,94 @@
+/* ddsp_b200.h -- C ABI of the B200-native DDSP synthesis hot path (libddsp_b200.so).
+ *
+ * The reference (kureta/ddsp-pytorch) is pure Python and has no FFI layer; its boundary for this
+ * path is the torch module API of model/ddsp/{harmonic_oscillator,filtered_noise,reverb}.py and
+ * loss/mss_loss.py.  Each entry point below is what a binding for one of those module methods
+ * calls (the ctypes binding is ddsp_pytorch_b200/_lib.py), and cites the
+ * reference lines it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to contiguous row-major fp32 unless stated otherwise;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls only enqueue work,
+ *     they never synchronise and never allocate;
+ *   - scratch/state buffers are caller-owned; sizes come from the *_bytes() queries;
+ *   - return value 0 = success, non-zero = error (ddsp_last_error() returns a message for the
+ *     calling thread).  Arguments are validated before anything is launched.
+ *   - shapes: B voices, T frames, hop samples per frame, N = T*hop samples, K harmonics,
+ *     NB noise bands (FIR length M = 2(NB-1) <= hop), L reverb taps.
+ */
+#ifndef DDSP_B200_H
+#define DDSP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDSP_B200_ABI_VERSION 1
+
+int         ddsp_abi_version(void);
+const char* ddsp_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Harmonic oscillator bank  --  OscillatorBank.forward, harmonic_oscillator.py:57-62
+ *   (prepare_harmonics :24-37, rescale :52-55, generate_phases :39-43, generate_signal :45-50)
+ * ------------------------------------------------------------------------------------------ */
+
+/* Bytes of the frame-rate state ddsp_osc_forward fills and ddsp_osc_backward reads:
+ * normalised masked amplitudes [B,T,K], their pre-normalisation sums [B,T], active-harmonic
+ * counts [B,T] and the fp64 phase prefix (cycles) at each segment start [B,T+1]. */
+size_t ddsp_osc_state_bytes(int B, int T, int K);
+
+/* y[B,N] (+)= sum_k a_up * c'_up * sin(phi_k).
+ *   f0 [B,T] Hz, c [B,T,K], a [B,T];  z_save [B,N] or NULL: harmonic sum before the loudness
+ *   multiply, needed by ddsp_osc_backward;  accumulate != 0 adds into y instead of overwriting. */
+int ddsp_osc_forward(const float* f0, const float* c, const float* a, float* y, float* z_save,
+                     void* state, int accumulate, int B, int T, int K, int hop, int sample_rate,
+                     void* stream);
+
+/* Scratch for ddsp_osc_backward: per-segment partial gradients [B,T+1,K,2] + [B,T+1,2]. */
+size_t ddsp_osc_backward_scratch_bytes(int B, int T, int K);
+
+/* Gradients of sum(g*y) w.r.t. c -> gc [B,T,K] and a -> ga [B,T]  (autograd of :24-50; f0 carries
+ * no gradient on the training path).  state/z_save are those of the forward call. */
+int ddsp_osc_backward(const float* g, const float* f0, const float* a, const float* z_save,
+                      const void* state, void* scratch, float* gc, float* ga, int B, int T, int K,
+                      int hop, int sample_rate, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Filtered noise  --  FilteredNoise.forward, filtered_noise.py:40-53
+ *   (amp_to_impulse_response :7-22, fft_convolve :25-32; per frame, tails dropped, no overlap-add)
+ * ------------------------------------------------------------------------------------------ */
+
+/* y[B,N] (+)= per-frame causal convolution of uniform noise with the windowed zero-phase FIR of H.
+ *   H [B,T,NB].  noise [B,T,hop] in [-1,1) or NULL: NULL draws the noise in-kernel with
+ *   Philox4x32-10, key = seed, counter = (j>>2, t, voice_offset + b, offset), word j&3,
+ *   u = (word>>8)*2^-24, noise = 2u-1  (oracle/philox.py is the CPU statement of this layout). */
+int ddsp_noise_forward(const float* H, const float* noise, float* y, int accumulate, uint64_t seed,
+                       uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop,
+                       void* stream);
+
+/* gH [B,T,NB] = d sum(g*y) / dH with the same noise (regenerated from the same seed/offset). */
+int ddsp_noise_backward(const float* g, const float* noise, float* gH, uint64_t seed,
+                        uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop,
+                        void* stream);
+
+/* The noise block itself [B,T,hop] (for tests of the Philox layout and for injecting it elsewhere). */
+int ddsp_noise_uniform(float* out, uint64_t seed, uint32_t offset, uint32_t voice_offset, int B,
+                       int T, int hop, void* stream);
+
+/* amp_to_impulse_response, filtered_noise.py:7-22: H [R,NB] -> ir [R,target]. */
+int ddsp_amp_to_impulse_response(const float* H, float* ir, int R, int NB, int target, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Measurement helper: dependent-free FFMA chains, for the measured FP32 roofline denominator.
+ * Each thread executes iters*64 FFMAs; out[grid*block] keeps the compiler honest.
+ * ------------------------------------------------------------------------------------------ */
+int ddsp_probe_fp32_fma(float* out, int blocks, int threads, int iters, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDSP_B200_H */
