@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""Benchmark of the DDSP synthesis hot path on B200 (contract: see the task statement / DESIGN.md §Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[3], SURVEY.md §8.0 cfg 4): 1024 voices x 4 s @ 48 kHz, hop 512 (T=375,
+N=192000), K=256 harmonics, NB=65 noise bands; one step = oscillator bank + filtered noise forward and
+backward (gradients to c, a, H from a fixed upstream gradient).  The 1024 voices are sharded over the
+ranks (strong scaling, no data-path collective).  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "synth_audio_samples_per_sec_fwd_bwd"
+UNIT = "samples/s"
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=10)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--voices", type=int, default=1024, help="total voices over all ranks")
+    p.add_argument("--harmonics", type=int, default=256)
+    p.add_argument("--bands", type=int, default=65)
+    p.add_argument("--sample-rate", type=int, default=48000)
+    p.add_argument("--seconds", type=float, default=4.0)
+    p.add_argument("--hop", type=int, default=512)
+    p.add_argument("--cpu-voices", type=int, default=2, help="voices in the bounded CPU sample")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-e2e", action="store_true")
+    return p.parse_args()
+
+
+def shapes(args):
+    T = int(args.seconds * args.sample_rate) // args.hop
+    return dict(B=args.voices, T=T, N=T * args.hop, K=args.harmonics, NB=args.bands, sr=args.sample_rate, hop=args.hop)
+
+
+def workload_config(args, sh, extra=None):
+    cfg = {"workload": f"cfg4 large-batch synthesis sweep: {sh['B']} voices x {args.seconds:g} s @ {sh['sr']} Hz, "
+                       f"K={sh['K']}, NB={sh['NB']}, hop={sh['hop']}; oscillator bank + filtered noise, fwd+bwd",
+           "voices": sh["B"], "frames": sh["T"], "samples_per_voice": sh["N"], "harmonics": sh["K"],
+           "noise_bands": sh["NB"], "sample_rate": sh["sr"], "hop": sh["hop"],
+           "cache": "per-step working set (c 0.39 GB + g/y/z 0.79 GB each at 1 GPU) exceeds the 126 MB L2; no explicit flush",
+           "parallelism": f"voices sharded over {args.gpus} rank(s), no collective"}
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.samples = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                                          "-i", str(index), "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                                         text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.time(), line.strip()))
+
+    def stop(self, t0: float, t1: float):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.06)
+        self.proc.terminate()
+        rows = [ln for (ts, ln) in self.samples if t0 <= ts <= t1 + 0.05] or [ln for (_, ln) in self.samples[-3:]]
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in rows:
+            parts = [x.strip() for x in ln.split(",")]
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (torch restatement of the reference's own CPU path) on host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_step(O, f0, c, a, H, g, sh):
+    """One fwd+bwd of oscillator + filtered noise exactly as the reference runs it on CPU, including its
+    CPU noise draw (filtered_noise.py:44-48)."""
+    c = c.detach().requires_grad_(True)
+    a = a.detach().requires_grad_(True)
+    H = H.detach().requires_grad_(True)
+    noise = torch.rand(H.shape[0], H.shape[1], sh["hop"]) * 2 - 1
+    y = O.oscillator_bank(f0, c, a, sh["K"], sh["sr"], sh["hop"]) + O.filtered_noise(H, sh["hop"], noise)
+    y.backward(g)
+    return y
+
+
+def cpu_measure(args, sh, steps: int, warmup: int):
+    from oracle import ddsp_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    Bc = max(1, min(args.cpu_voices, sh["B"]))
+    f0, c, a, H = O.synthetic_controls(Bc, sh["T"], sh["K"], sh["NB"], sh["sr"], sh["hop"], seed=1234 + 4)
+    g = torch.randn(Bc, sh["N"], generator=torch.Generator().manual_seed(99))
+    for _ in range(warmup):
+        cpu_step(O, f0, c, a, H, g, sh)
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        cpu_step(O, f0, c, a, H, g, sh)
+        times.append(time.perf_counter() - t0)
+    best = min(times)
+    return {"value": Bc * sh["N"] / best, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{Bc} of the {sh['B']} voices (same shapes), oracle/ddsp_oracle.py in fp32 torch eager, "
+                      f"best of {steps} after {warmup} warm-up; median {statistics.median(times):.2f} s/step",
+            "ms_per_step": best * 1e3, "median_ms_per_step": statistics.median(times) * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sh = shapes(args)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
+    # bounded: each step is a cpu-voices sample (~seconds); cap the count so the run ends within minutes
+    steps_run, warm_run = min(steps, 5), min(warmup, 1)
+    res = cpu_measure(args, sh, steps_run, warm_run)
+    line = {"impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, sh, {"steps_run": steps_run, "warmup_run": warm_run}),
+            "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def active_harmonic_samples(f0, K, sr, hop):
+    """Sum over (voice, hop segment) of samples x harmonics that are not Nyquist-masked in BOTH frames of the
+    segment -- the harmonic-samples the synthesis / gradient kernels actually evaluate."""
+    B, T = f0.shape[0], f0.shape[1]
+    k = torch.arange(1, K + 1, device=f0.device, dtype=torch.float32)
+    kact = ((k.view(1, 1, -1) * f0.view(B, T, 1)) <= float(sr // 2)).sum(-1)              # [B,T], mask is monotone in k
+    left = torch.cat([kact[:, :1], kact], dim=1)                                          # segment s: frames s-1 | s
+    right = torch.cat([kact, kact[:, -1:]], dim=1)
+    kmax = torch.maximum(left, right).double()                                            # [B,T+1]
+    n = torch.full((T + 1,), float(hop), dtype=torch.float64, device=f0.device)
+    n[0] = n[-1] = hop / 2
+    return float((kmax * n).sum())
+
+
+def time_call(fn, reps=10, warm=2):
+    for _ in range(warm):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def run_b200(args):
+    import torch.distributed as dist
+    import ddsp_pytorch_b200 as d
+    from ddsp_pytorch_b200 import _lib, ops
+    from oracle import ddsp_oracle as O            # input generator only (synthetic_controls); never on the timed path
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl b200 needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    sh = shapes(args)
+    assert sh["B"] % world == 0, "voices must divide over ranks"
+    Bl = sh["B"] // world
+    T, N, K, NB, sr, hop = sh["T"], sh["N"], sh["K"], sh["NB"], sh["sr"], sh["hop"]
+    conf = d.Config(sample_rate=sr, hop_length=hop, n_harmonics=K, n_noise_filters=NB)
+
+    # ---- synthetic inputs, generated on the host, this rank's voices only ------------
+    f0h, ch, ah, Hh = O.synthetic_controls(Bl, T, K, NB, sr, hop, seed=1234 + 4, voice_offset=rank * Bl)
+    gh = torch.randn(Bl, N, generator=torch.Generator().manual_seed(99 + rank))
+    host = [t.pin_memory() for t in (f0h, ch, ah, Hh, gh)]
+    f0, c, a, H, g = (t.to(dev) for t in host)
+    c.requires_grad_(True); a.requires_grad_(True); H.requires_grad_(True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    seed, voff = 7, rank * Bl
+    counter = [0]
+
+    def step():
+        """resident inputs -> y = noise(H); y += osc(f0,c,a); backward from g.  6 launches of this repo's kernels."""
+        c.grad = a.grad = H.grad = None
+        y = ops.filtered_noise(H, hop, seed=seed, offset=counter[0], voice_offset=voff)
+        y = ops.oscillator_bank(f0, c, a, sr, hop, out=y)
+        y.backward(g)
+        counter[0] += 1
+        return y
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_load0 = time.time()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop(t_load0, time.time()) if sampler else None
+    value = sh["B"] * N * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the module API with host buffers -----------------------------------
+    e2e = None
+    if not args.no_e2e:
+        bank, fnoise = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=seed, voice_offset=voff)
+        outs = [torch.empty(s, dtype=torch.float32).pin_memory() for s in ((Bl, T, K), (Bl, T, 1), (Bl, T, NB))]
+        h2d = sum(t.numel() * 4 for t in host)
+        d2h = sum(t.numel() * 4 for t in outs)
+
+        def e2e_step():
+            f0d, cd, ad, Hd, gd = (t.to(dev, non_blocking=True) for t in host)
+            cd.requires_grad_(True); ad.requires_grad_(True); Hd.requires_grad_(True)
+            ctrl = {"f0": f0d, "c": cd, "a": ad, "H": Hd}
+            y = bank(ctrl) + fnoise(ctrl)                     # decoder.py:129-132
+            y.backward(gd)
+            for o, t in zip(outs, (cd.grad, ad.grad, Hd.grad)):
+                o.copy_(t, non_blocking=True)
+            torch.cuda.current_stream().synchronize()         # the host now owns the gradients
+
+        for _ in range(max(args.warmup, 3)):
+            e2e_step()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            e2e_step()
+        e1.record()
+        barrier()
+        ems = max_over_ranks(e0.elapsed_time(e1))
+        e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+               "d2h_bytes_per_step": d2h * world, "ms_per_step": ems / args.steps,
+               "path": "pinned host f0,c,a,H,g -> OscillatorBank + FilteredNoise modules (+ torch add) -> backward -> grads to pinned host"}
+
+    # ---- per-kernel device times (rank 0's shard) and the roofline of the dominant kernel -------
+    lib = _lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    state = torch.empty(lib.ddsp_osc_state_bytes(Bl, T, K), dtype=torch.uint8, device=dev)
+    scratch = torch.empty(lib.ddsp_osc_backward_scratch_bytes(Bl, T, K), dtype=torch.uint8, device=dev)
+    y = torch.empty(Bl, N, device=dev); z = torch.empty(Bl, N, device=dev)
+    gc = torch.empty(Bl, T, K, device=dev); ga = torch.empty(Bl, T, device=dev); gH = torch.empty(Bl, T, NB, device=dev)
+    P = lambda t: t.data_ptr()  # noqa: E731
+    cd_, ad_, Hd_ = c.detach(), a.detach(), H.detach()
+    calls = {
+        "osc_prepare_kernel": lambda: _lib.call("ddsp_osc_prepare", P(f0), P(cd_), P(state), Bl, T, K, hop, sr, st),
+        "osc_synth_kernel": lambda: _lib.call("ddsp_osc_synthesize", P(f0), P(ad_), P(state), P(y), P(z), 0, Bl, T, K, hop, sr, st),
+        "osc_grad_kernel": lambda: _lib.call("ddsp_osc_grad_segments", P(g), P(f0), P(ad_), P(z), P(state), P(scratch), Bl, T, K, hop, sr, st),
+        "osc_finalize_kernel": lambda: _lib.call("ddsp_osc_grad_finalize", P(f0), P(state), P(scratch), P(gc), P(ga), Bl, T, K, hop, sr, st),
+        "noise_fwd_kernel": lambda: _lib.call("ddsp_noise_forward", P(Hd_), None, P(y), 0, seed, 0, voff, Bl, T, NB, hop, st),
+        "noise_bwd_kernel": lambda: _lib.call("ddsp_noise_backward", P(g), None, P(gH), seed, 0, voff, Bl, T, NB, hop, st),
+    }
+    kernels_ms = {name: time_call(fn) for name, fn in calls.items()}
+    fp32_peak = ops.probe_fp32_fma_tflops()
+    active = active_harmonic_samples(f0.view(Bl, T), K, sr, hop)
+    dom = max(kernels_ms, key=kernels_ms.get)
+    # SURVEY §8d algorithmic work per harmonic-sample: 6 flops forward, 12 flops backward
+    flops_per_hs = {"osc_synth_kernel": 6.0, "osc_grad_kernel": 12.0}.get(dom)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+    except (OSError, ValueError):
+        pass
+    roofline = None
+    if flops_per_hs:
+        ach = flops_per_hs * active / (kernels_ms[dom] * 1e-3) / 1e12
+        roofline = {"kernel": dom, "bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
+                    "traffic": traffic, "launch_ms": kernels_ms[dom],
+                    "peak_source": "FFMA-chain probe (ddsp_probe_fp32_fma) measured in this run; MEASURED_PEAKS.json has no FP32 figure",
+                    "work": f"{flops_per_hs:g} flop x {active:.4g} active harmonic-samples on this rank "
+                            f"(nominal K would be {Bl * N * K:.4g}; Nyquist-masked harmonics are skipped)",
+                    "achieved_if_nominal_K": flops_per_hs * Bl * N * K / (kernels_ms[dom] * 1e-3) / 1e12,
+                    "hbm": {"algorithmic_bytes": 4.0 * (Bl * N * 2 + Bl * T * (K + 2)),
+                            "achieved_GBps": 4.0 * (Bl * N * 2 + Bl * T * (K + 2)) / (kernels_ms[dom] * 1e-3) / 1e9,
+                            "peak_GBps": peaks.get("hbm_gbs")}}
+
+    if world > 1:
+        dist.barrier(device_ids=[local])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        r = cpu_measure(args, sh, steps=2, warmup=1)
+        cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(args, sh), "clocks": clocks, "e2e": e2e, "gpu_launches": 6 * args.steps,
+            "roofline": roofline, "cpu_baseline": cpu, "kernels_ms": kernels_ms, "fp32_fma_peak_tflops_measured": fp32_peak}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a_ = parse_args()
+    if a_.impl == "reference":
+        run_reference(a_)
+    else:
+        run_b200(a_)

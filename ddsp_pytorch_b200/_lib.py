@@ -17,6 +17,10 @@ SIGNATURES = {
     "ddsp_last_error": (C.c_char_p, []),
     "ddsp_osc_state_bytes": (_sz, [_i, _i, _i]),
     "ddsp_osc_forward": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "ddsp_osc_prepare": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ddsp_osc_synthesize": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "ddsp_osc_grad_segments": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ddsp_osc_grad_finalize": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ddsp_osc_backward_scratch_bytes": (_sz, [_i, _i, _i]),
     "ddsp_osc_backward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ddsp_noise_forward": (_i, [_p, _p, _p, _i, _u64, _u32, _u32, _i, _i, _i, _i, _p]),

@@ -411,14 +411,23 @@ extern "C" size_t ddsp_osc_backward_scratch_bytes(int B, int T, int K) {
     return align_up(sizeof(float2) * (size_t)B * (T + 1) * K, 256) + align_up(sizeof(float2) * (size_t)B * (T + 1), 256);
 }
 
-extern "C" int ddsp_osc_forward(const float* f0, const float* c, const float* a, float* y, float* z_save, void* state,
-                                int accumulate, int B, int T, int K, int hop, int sample_rate, void* stream) {
-    if (check_osc_shape("ddsp_osc_forward", B, T, K, hop, sample_rate)) return 1;
-    DDSP_REQUIRE(f0 && c && a && y && state, "ddsp_osc_forward: null pointer argument");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
+extern "C" int ddsp_osc_prepare(const float* f0, const float* c, void* state, int B, int T, int K, int hop, int sample_rate,
+                                void* stream) {
+    if (check_osc_shape("ddsp_osc_prepare", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(f0 && c && state, "ddsp_osc_prepare: null pointer argument");
     const OscState S = carve_osc_state(state, B, T, K);
-    osc_prepare_kernel<<<B, PREP_THREADS, 0, st>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, T, K, hop, sample_rate);
+    osc_prepare_kernel<<<B, PREP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, T, K,
+                                                                                 hop, sample_rate);
     DDSP_CHECK_LAUNCH("osc_prepare_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_osc_synthesize(const float* f0, const float* a, const void* state, float* y, float* z_save, int accumulate,
+                                   int B, int T, int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_synthesize", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(f0 && a && y && state, "ddsp_osc_synthesize: null pointer argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
     const int R = pick_R(hop, 4);
     const dim3 grid(T + 1, B);
     const size_t smem = sizeof(float2) * ((K + 1) & ~1);
@@ -434,6 +443,13 @@ extern "C" int ddsp_osc_forward(const float* f0, const float* c, const float* a,
 #undef LAUNCH_SYNTH
     DDSP_CHECK_LAUNCH("osc_synth_kernel");
     return 0;
+}
+
+extern "C" int ddsp_osc_forward(const float* f0, const float* c, const float* a, float* y, float* z_save, void* state,
+                                int accumulate, int B, int T, int K, int hop, int sample_rate, void* stream) {
+    int rc = ddsp_osc_prepare(f0, c, state, B, T, K, hop, sample_rate, stream);
+    if (rc) return rc;
+    return ddsp_osc_synthesize(f0, a, state, y, z_save, accumulate, B, T, K, hop, sample_rate, stream);
 }
 
 template <int R>
@@ -452,28 +468,45 @@ static int launch_grad(const float* g, const float* a, const float* f0, const fl
     return 0;
 }
 
-extern "C" int ddsp_osc_backward(const float* g, const float* f0, const float* a, const float* z_save, const void* state,
-                                 void* scratch, float* gc, float* ga, int B, int T, int K, int hop, int sample_rate,
-                                 void* stream) {
-    if (check_osc_shape("ddsp_osc_backward", B, T, K, hop, sample_rate)) return 1;
-    DDSP_REQUIRE(g && f0 && a && z_save && state && scratch && gc && ga, "ddsp_osc_backward: null pointer argument");
+static float2* scratch_gaseg(void* scratch, int B, int T, int K) {
+    return reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) + align_up(sizeof(float2) * (size_t)B * (T + 1) * K, 256));
+}
+
+extern "C" int ddsp_osc_grad_segments(const float* g, const float* f0, const float* a, const float* z_save, const void* state,
+                                      void* scratch, int B, int T, int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_grad_segments", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(g && f0 && a && z_save && state && scratch, "ddsp_osc_grad_segments: null pointer argument");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
     float2* gseg = reinterpret_cast<float2*>(scratch);
-    float2* gaseg = reinterpret_cast<float2*>(reinterpret_cast<char*>(scratch) +
-                                              align_up(sizeof(float2) * (size_t)B * (T + 1) * K, 256));
-    int rc;
+    float2* gaseg = scratch_gaseg(scratch, B, T, K);
     switch (pick_R(hop, 8)) {
-        case 8: rc = launch_grad<8>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
-        case 4: rc = launch_grad<4>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
-        case 2: rc = launch_grad<2>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
-        default: rc = launch_grad<1>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st); break;
+        case 8: return launch_grad<8>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
+        case 4: return launch_grad<4>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
+        case 2: return launch_grad<2>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
+        default: return launch_grad<1>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
     }
-    if (rc) return rc;
+}
+
+extern "C" int ddsp_osc_grad_finalize(const float* f0, const void* state, const void* scratch, float* gc, float* ga, int B,
+                                      int T, int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_grad_finalize", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(f0 && state && scratch && gc && ga, "ddsp_osc_grad_finalize: null pointer argument");
+    const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
+    const float2* gseg = reinterpret_cast<const float2*>(scratch);
+    const float2* gaseg = scratch_gaseg(const_cast<void*>(scratch), B, T, K);
     const long long frames = (long long)B * T;
     const int wpb = 8;
-    osc_finalize_kernel<<<(unsigned)((frames + wpb - 1) / wpb), wpb * 32, 0, st>>>(gseg, gaseg, S.cn, S.csum, S.kact, f0, gc,
-                                                                                 ga, B, T, K, sample_rate);
+    osc_finalize_kernel<<<(unsigned)((frames + wpb - 1) / wpb), wpb * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        gseg, gaseg, S.cn, S.csum, S.kact, f0, gc, ga, B, T, K, sample_rate);
     DDSP_CHECK_LAUNCH("osc_finalize_kernel");
     return 0;
+}
+
+extern "C" int ddsp_osc_backward(const float* g, const float* f0, const float* a, const float* z_save, const void* state,
+                                 void* scratch, float* gc, float* ga, int B, int T, int K, int hop, int sample_rate,
+                                 void* stream) {
+    int rc = ddsp_osc_grad_segments(g, f0, a, z_save, state, scratch, B, T, K, hop, sample_rate, stream);
+    if (rc) return rc;
+    return ddsp_osc_grad_finalize(f0, state, scratch, gc, ga, B, T, K, hop, sample_rate, stream);
 }

@@ -48,6 +48,12 @@ int ddsp_osc_forward(const float* f0, const float* c, const float* a, float* y, 
                      void* state, int accumulate, int B, int T, int K, int hop, int sample_rate,
                      void* stream);
 
+/* The two launches of ddsp_osc_forward on their own (frame-rate preparation; sample-rate synthesis). */
+int ddsp_osc_prepare(const float* f0, const float* c, void* state, int B, int T, int K, int hop,
+                     int sample_rate, void* stream);
+int ddsp_osc_synthesize(const float* f0, const float* a, const void* state, float* y, float* z_save,
+                        int accumulate, int B, int T, int K, int hop, int sample_rate, void* stream);
+
 /* Scratch for ddsp_osc_backward: per-segment partial gradients [B,T+1,K,2] + [B,T+1,2]. */
 size_t ddsp_osc_backward_scratch_bytes(int B, int T, int K);
 
@@ -56,6 +62,14 @@ size_t ddsp_osc_backward_scratch_bytes(int B, int T, int K);
 int ddsp_osc_backward(const float* g, const float* f0, const float* a, const float* z_save,
                       const void* state, void* scratch, float* gc, float* ga, int B, int T, int K,
                       int hop, int sample_rate, void* stream);
+
+/* The two launches of ddsp_osc_backward on their own (per-segment sums over samples; frame-rate gather
+ * + backward of mask/normalise). */
+int ddsp_osc_grad_segments(const float* g, const float* f0, const float* a, const float* z_save,
+                           const void* state, void* scratch, int B, int T, int K, int hop,
+                           int sample_rate, void* stream);
+int ddsp_osc_grad_finalize(const float* f0, const void* state, const void* scratch, float* gc,
+                           float* ga, int B, int T, int K, int hop, int sample_rate, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Filtered noise  --  FilteredNoise.forward, filtered_noise.py:40-53
