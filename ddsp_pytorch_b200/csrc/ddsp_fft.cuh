@@ -1,0 +1,77 @@
+// Shared-memory complex FFT for power-of-two sizes (Stockham autosort, radix 4 with one radix-2 pass when
+// log2(n) is odd).  Used by the long convolution of the reverb (reverb.py:31-38 via fft_convolve,
+// filtered_noise.py:25-32) and by the STFT front end of the spectral loss (mss_loss.py:23-27), where the
+// reference calls cuFFT through torch.fft / torch.stft.
+//
+//   * data: float2[n] ping-pong pair in shared memory, natural order in, natural order out;
+//   * twiddles: float2 tw[n] in shared memory, tw[q] = (cos(2 pi q/n), -sin(2 pi q/n)), filled once per
+//     CTA by fft_fill_twiddles (sincospif on an exactly representable argument: <= 1 ulp);
+//   * a "group" of `gsize` threads (any divisor layout of the CTA) owns one transform; every pass ends
+//     with a CTA-wide __syncthreads(), so all groups of a CTA must transform the same n together.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace ddsp {
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+__device__ __forceinline__ float2 cmul_conj(float2 a, float2 b) {   // a * conj(b)
+    return make_float2(fmaf(a.x, b.x, a.y * b.y), fmaf(a.y, b.x, -a.x * b.y));
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+
+__device__ __forceinline__ void fft_fill_twiddles(float2* tw, int n) {
+    const float inv = 2.0f / (float)n;
+    for (int q = threadIdx.x; q < n; q += blockDim.x) {
+        float s, c;
+        sincospif((float)q * inv, &s, &c);
+        tw[q] = make_float2(c, -s);
+    }
+}
+
+// One transform of size n by the `gsize` threads gtid = 0..gsize-1.  `a` holds the input; returns the buffer
+// (a or b) that holds the output.  INV = true computes the unnormalised inverse (conjugated twiddles).
+template <bool INV>
+__device__ __forceinline__ float2* block_fft(float2* a, float2* b, const float2* __restrict__ tw, int n, int gtid, int gsize) {
+    int p = 1;
+    int log2n = 31 - __clz(n);
+    if (log2n & 1) {                                   // radix-2 pass, p = 1 (no twiddle)
+        const int t = n >> 1;
+        for (int i = gtid; i < t; i += gsize) {
+            const float2 u0 = a[i], u1 = a[i + t];
+            b[2 * i] = cadd(u0, u1);
+            b[2 * i + 1] = csub(u0, u1);
+        }
+        __syncthreads();
+        float2* s = a; a = b; b = s;
+        p = 2;
+    }
+    const int t = n >> 2;
+    for (; p < n; p <<= 2) {
+        const int tstep = n / (4 * p);                 // tw index step: w_{4p}^k = tw[k * n/(4p)]
+        for (int i = gtid; i < t; i += gsize) {
+            const int k = i & (p - 1);
+            const int j = ((i - k) << 2) + k;
+            float2 w1 = tw[k * tstep], w2 = tw[2 * k * tstep], w3 = tw[3 * k * tstep];
+            if (INV) { w1.y = -w1.y; w2.y = -w2.y; w3.y = -w3.y; }
+            const float2 u0 = a[i];
+            const float2 u1 = cmul(a[i + t], w1);
+            const float2 u2 = cmul(a[i + 2 * t], w2);
+            const float2 u3 = cmul(a[i + 3 * t], w3);
+            const float2 v0 = cadd(u0, u2), v1 = csub(u0, u2), v2 = cadd(u1, u3);
+            const float2 d = csub(u1, u3);
+            const float2 v3 = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);   // (+/-)i * (u1-u3)
+            b[j] = cadd(v0, v2);
+            b[j + p] = cadd(v1, v3);
+            b[j + 2 * p] = csub(v0, v2);
+            b[j + 3 * p] = csub(v1, v3);
+        }
+        __syncthreads();
+        float2* s = a; a = b; b = s;
+    }
+    return a;
+}
+
+}  // namespace ddsp

@@ -1,0 +1,189 @@
+// Multi-scale spectral loss for sm_100a -- replaces SSSLoss / MSSLoss (mss_loss.py:11-68).
+//
+// The reference runs, per scale and per signal, torchaudio Spectrogram (reflect pad + torch.stft through
+// cuFFT + abs().pow(2)) and then ~8 elementwise / reduction passes over a 2-4x oversampled spectrogram,
+// and autograd replays all of it backwards.  Here one kernel per scale does everything for a frame while
+// it sits in shared memory:
+//   reflect-pad gather + periodic Hann -> ONE complex FFT for the (pred, true) pair of a frame
+//   (z = w*x_pred + i w*x_true, split by Hermitian symmetry) -> power spectra -> both L1 terms
+//   -> d loss / d S_pred -> inverse FFT of 2*X_pred*dS (upper half zero, real part) -> window ->
+//   overlap-add into d loss / d x_pred with the adjoint of the reflect pad.
+// The spectrograms never reach HBM; the gradient is produced in the forward pass (the loss is a scalar, so
+// backward is one multiply by the upstream scalar).
+#include "ddsp_common.cuh"
+#include "ddsp_fft.cuh"
+
+namespace ddsp {
+
+constexpr int MSS_THREADS = 256;
+constexpr int MSS_ITERS = 4;       // frame batches per CTA (amortises the twiddle / window tables)
+
+__device__ __forceinline__ int reflect_index(int p, int N) {
+    if (p < 0) p = -p;
+    if (p >= N) p = 2 * (N - 1) - p;
+    return p;
+}
+
+struct MssGeom {
+    int gs;       // threads per frame
+    int fc;       // frames processed concurrently by a CTA
+};
+
+__host__ __device__ inline MssGeom mss_geom(int n) {
+    MssGeom g;
+    g.gs = n / 4 < MSS_THREADS ? (n / 4 < 1 ? 1 : n / 4) : MSS_THREADS;
+    g.fc = MSS_THREADS / g.gs;
+    return g;
+}
+
+__host__ __device__ inline size_t mss_smem_bytes(int n) {
+    const MssGeom g = mss_geom(n);
+    return sizeof(float2) * n /*tw*/ + sizeof(float) * n /*window*/ + sizeof(float2) * 2 * (size_t)n * g.fc;
+}
+
+__global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __restrict__ xp, const float* __restrict__ xt,
+                                                                double* __restrict__ loss, double* __restrict__ terms,
+                                                                float* __restrict__ gx, int N, int n, int hop, int F,
+                                                                double inv_count, double alpha_d, float eps) {
+    extern __shared__ __align__(16) unsigned char mss_raw[];
+    float2* tw = reinterpret_cast<float2*>(mss_raw);
+    float* win = reinterpret_cast<float*>(tw + n);
+    float2* bufs = reinterpret_cast<float2*>(win + n);
+    __shared__ double red[2][MSS_THREADS / 32];
+
+    const MssGeom geo = mss_geom(n);
+    const int tid = threadIdx.x;
+    const int grp = tid / geo.gs, gtid = tid % geo.gs;
+    const int b = blockIdx.y;
+    float2* A = bufs + (size_t)grp * 2 * n;
+    float2* Bf = A + n;
+    const float* xpb = xp + (size_t)b * N;
+    const float* xtb = xt + (size_t)b * N;
+    float* gxb = gx ? gx + (size_t)b * N : nullptr;
+
+    fft_fill_twiddles(tw, n);
+    for (int m = tid; m < n; m += MSS_THREADS) win[m] = 0.5f - 0.5f * cospif(2.0f * (float)m / (float)n);   // periodic Hann
+    __syncthreads();
+
+    const float w_lin = (float)inv_count, w_log = (float)(alpha_d * inv_count);
+    const float inv_ln2 = 1.4426950408889634f;
+    double acc_lin = 0.0, acc_log = 0.0;
+    const int half = n / 2;
+    for (int it = 0; it < MSS_ITERS; ++it) {
+        const int f = (blockIdx.x * MSS_ITERS + it) * geo.fc + grp;
+        const bool live = f < F;                       // dead groups still walk through every barrier
+        const int p0 = f * hop - half;
+        for (int m = gtid; m < n; m += geo.gs) {
+            float2 v = make_float2(0.f, 0.f);
+            if (live) {
+                const int idx = reflect_index(p0 + m, N);
+                const float w = win[m];
+                v = make_float2(w * xpb[idx], w * xtb[idx]);
+            }
+            A[m] = v;
+        }
+        __syncthreads();
+        float2* Z = block_fft<false>(A, Bf, tw, n, gtid, geo.gs);
+        float2* Y = (Z == A) ? Bf : A;
+        for (int k = gtid; k < n; k += geo.gs) {
+            float2 yk = make_float2(0.f, 0.f);
+            if (k <= half && live) {
+                const float2 zk = Z[k], zn = Z[(n - k) & (n - 1)];
+                // X_pred = (Z_k + conj Z_{n-k})/2 ;  X_true = (Z_k - conj Z_{n-k})/(2i)
+                const float pr = 0.5f * (zk.x + zn.x), pi = 0.5f * (zk.y - zn.y);
+                const float tr = 0.5f * (zk.y + zn.y), ti = -0.5f * (zk.x - zn.x);
+                const float sp = pr * pr + pi * pi, st = tr * tr + ti * ti;        // power=2 spectrogram
+                const float dl = sp - st;
+                const float lp = log2f(sp + eps), lt = log2f(st + eps);
+                const float dq = lp - lt;
+                acc_lin += (double)fabsf(dl);
+                acc_log += (double)fabsf(dq);
+                const float sl = (dl > 0.f) - (dl < 0.f), sq = (dq > 0.f) - (dq < 0.f);
+                const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);  // d loss / d S_pred
+                yk = make_float2(2.f * pr * gs_, 2.f * pi * gs_);
+            }
+            if (gxb) Y[k] = yk;
+        }
+        __syncthreads();
+        if (gxb) {
+            const float2* R = block_fft<true>(Y, Z, tw, n, gtid, geo.gs);
+            if (live)
+                for (int m = gtid; m < n; m += geo.gs) atomicAdd(&gxb[reflect_index(p0 + m, N)], R[m].x * win[m]);
+            __syncthreads();
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        acc_lin += __shfl_xor_sync(0xffffffffu, acc_lin, o);
+        acc_log += __shfl_xor_sync(0xffffffffu, acc_log, o);
+    }
+    if ((tid & 31) == 0) { red[0][tid >> 5] = acc_lin; red[1][tid >> 5] = acc_log; }
+    __syncthreads();
+    if (tid == 0) {
+        double l = 0.0, q = 0.0;
+        for (int w = 0; w < MSS_THREADS / 32; ++w) { l += red[0][w]; q += red[1][w]; }
+        atomicAdd(&terms[0], l);
+        atomicAdd(&terms[1], q);
+        atomicAdd(loss, (l + alpha_d * q) * inv_count);
+    }
+}
+
+__global__ void scale_by_scalar_kernel(const float* __restrict__ in, const float* __restrict__ s, float* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i] * s[0];
+}
+
+__global__ void double_to_float_kernel(const double* __restrict__ in, float* __restrict__ out) { out[0] = (float)in[0]; }
+
+}  // namespace ddsp
+
+using namespace ddsp;
+
+extern "C" int64_t ddsp_mss_count(int B, int N, int n_fft, int hop) {
+    if (B < 1 || N < 1 || n_fft < 2 || hop < 1) return 0;
+    return (int64_t)B * (n_fft / 2 + 1) * (1 + N / hop);
+}
+
+extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double* loss_terms, float* loss_f32, float* gx,
+                                const int* n_ffts_host, const int* hops_host, int n_scales, float alpha, float eps, int B, int N,
+                                void* stream) {
+    DDSP_REQUIRE(x_pred && x_true && loss_terms && n_ffts_host && hops_host, "ddsp_mss_forward: null pointer argument");
+    DDSP_REQUIRE(B >= 1 && B <= 65535 && N >= 2 && n_scales >= 1 && n_scales <= 64, "ddsp_mss_forward: bad B/N/n_scales");
+    for (int s = 0; s < n_scales; ++s) {
+        const int n = n_ffts_host[s], hop = hops_host[s];
+        DDSP_REQUIRE(n >= 4 && n <= 4096 && (n & (n - 1)) == 0, "ddsp_mss_forward: n_fft=%d must be a power of two in [4,4096]", n);
+        DDSP_REQUIRE(hop >= 1, "ddsp_mss_forward: hop=%d must be positive", hop);
+        DDSP_REQUIRE(n / 2 < N, "ddsp_mss_forward: reflect padding n_fft/2=%d needs a signal longer than that (N=%d)", n / 2, N);
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cudaError_t e = cudaMemsetAsync(loss_terms, 0, sizeof(double) * (1 + 2 * (size_t)n_scales), st);
+    if (e == cudaSuccess && gx) e = cudaMemsetAsync(gx, 0, sizeof(float) * (size_t)B * N, st);
+    DDSP_REQUIRE(e == cudaSuccess, "ddsp_mss_forward: memset failed: %s", cudaGetErrorString(e));
+    for (int s = 0; s < n_scales; ++s) {
+        const int n = n_ffts_host[s], hop = hops_host[s];
+        const int F = 1 + N / hop;
+        const MssGeom g = mss_geom(n);
+        const size_t smem = mss_smem_bytes(n);
+        if (smem > 48 * 1024) {
+            e = cudaFuncSetAttribute(mss_scale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            DDSP_REQUIRE(e == cudaSuccess, "mss_scale_kernel: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
+        }
+        const double count = (double)ddsp_mss_count(B, N, n, hop);
+        const int per_cta = g.fc * MSS_ITERS;
+        mss_scale_kernel<<<dim3((F + per_cta - 1) / per_cta, B), MSS_THREADS, smem, st>>>(
+            x_pred, x_true, loss_terms, loss_terms + 1 + 2 * s, gx, N, n, hop, F, 1.0 / count, (double)alpha, eps);
+        DDSP_CHECK_LAUNCH("mss_scale_kernel");
+    }
+    if (loss_f32) {
+        double_to_float_kernel<<<1, 1, 0, st>>>(loss_terms, loss_f32);
+        DDSP_CHECK_LAUNCH("double_to_float_kernel");
+    }
+    return 0;
+}
+
+extern "C" int ddsp_mss_backward(const float* gloss, const float* gx_saved, float* gx_out, int B, int N, void* stream) {
+    DDSP_REQUIRE(gloss && gx_saved && gx_out && B >= 1 && N >= 1, "ddsp_mss_backward: bad arguments");
+    const size_t n = (size_t)B * N;
+    scale_by_scalar_kernel<<<(unsigned)((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(gx_saved, gloss, gx_out, n);
+    DDSP_CHECK_LAUNCH("scale_by_scalar_kernel");
+    return 0;
+}

@@ -1,0 +1,376 @@
+// Learned reverb for sm_100a -- replaces Reverb (reverb.py:9-49) and the long-kernel use of fft_convolve
+// (filtered_noise.py:25-32).
+//
+// The reference pads signal and kernel to 2N and runs three monolithic FFTs of size 2N = 176128..384000
+// (non power of two) per call.  Here the causal, truncated convolution y[n] = sum_q ir[q] x[n-q] is a
+// uniformly partitioned overlap-save convolution with P = 2048-sample blocks and 4096-point complex FFTs
+// that live entirely in shared memory:
+//   conv_spectra_kernel   X[b2,i,:] = FFT_4096(x[(i-1)P .. (i+1)P))            one CTA per block i
+//   conv_mac_ifft_kernel  y block i = last P samples of IFFT(sum_j X[i-j] * H[j])
+// Two voices share one complex transform (z = x_a + i x_b): convolution with a REAL kernel is real-linear,
+// so the inverse transform returns y_a + i y_b with no split/merge pass at all.
+// Backward: gx is the same convolution run on the time-reversed gradient; gir is a frequency-domain
+// cross-correlation sum over voices and blocks (conv_gir_kernel -> deterministic two-stage reduction ->
+// conv_gir_finish_kernel); build_impulse has its own forward/backward kernels.
+#include "ddsp_common.cuh"
+#include "ddsp_fft.cuh"
+
+namespace ddsp {
+
+constexpr int CONV_P = 2048;            // new samples per block
+constexpr int CONV_N2 = 2 * CONV_P;     // FFT size
+constexpr int CONV_THREADS = 512;
+constexpr int GIR_CHUNKS = 32;          // partial sums over voice pairs kept apart for a fixed-order reduction
+constexpr int GIR_NP = 24;              // IR partitions handled per pass of the gir kernel
+
+struct ConvPlan {
+    int B2, nblk, np;
+    size_t off_H, off_S0, off_S1, off_part, total;
+};
+
+static ConvPlan conv_plan(int B, int N, int Lk) {
+    ConvPlan p;
+    p.B2 = (B + 1) / 2;
+    p.nblk = (N + CONV_P - 1) / CONV_P;
+    const int Le = Lk < N ? Lk : N;                     // taps at lags >= N never reach an output (reverb.py:34 crops)
+    p.np = (Le + CONV_P - 1) / CONV_P;
+    const size_t spec = sizeof(float2) * (size_t)p.B2 * p.nblk * CONV_N2;
+    p.off_H = 0;
+    p.off_S0 = align_up(sizeof(float2) * (size_t)p.np * CONV_N2, 256);
+    p.off_S1 = p.off_S0 + align_up(spec, 256);
+    p.off_part = p.off_S1 + align_up(spec, 256);
+    p.total = p.off_part + align_up(sizeof(float2) * (size_t)GIR_CHUNKS * p.np * CONV_N2, 256);
+    return p;
+}
+
+// ------------------------------------------------------------------------------------------------
+// build_impulse (reverb.py:24-29) and its backward
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float softplus_f(float x) { return x > 20.f ? x : log1pf(expf(x)); }   // torch threshold
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.f / (1.f + expf(-x)); }
+
+__global__ void reverb_impulse_kernel(const float* __restrict__ noise, const float* __restrict__ t, const float* __restrict__ decay,
+                                      const float* __restrict__ wet, float* __restrict__ ir, int L) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L) return;
+    const float sp = softplus_f(-decay[0]), sg = sigmoid_f(wet[0]);
+    ir[i] = i == 0 ? 1.f : noise[i] * expf(-sp * t[i] * 500.f) * sg;
+}
+
+__global__ void __launch_bounds__(1024) reverb_impulse_bwd_kernel(const float* __restrict__ gir, const float* __restrict__ noise,
+                                                                  const float* __restrict__ t, const float* __restrict__ decay,
+                                                                  const float* __restrict__ wet, float* __restrict__ gnoise,
+                                                                  float* __restrict__ gdecay, float* __restrict__ gwet, int L) {
+    __shared__ double red[2][32];
+    const float sp = softplus_f(-decay[0]), sg = sigmoid_f(wet[0]), sgd = sigmoid_f(-decay[0]);
+    double aw = 0.0, ad = 0.0;
+    for (int i = threadIdx.x; i < L; i += blockDim.x) {
+        float gn = 0.f;
+        if (i > 0) {                                      // ir[0] is overwritten with 1 (:28): no gradient
+            const float env = expf(-sp * t[i] * 500.f), g = gir[i];
+            gn = g * env * sg;
+            const float gne = g * noise[i] * env;
+            aw += (double)(gne * sg * (1.f - sg));
+            ad += (double)(gne * sg * t[i] * 500.f * sgd);
+        }
+        gnoise[i] = gn;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        aw += __shfl_xor_sync(0xffffffffu, aw, o);
+        ad += __shfl_xor_sync(0xffffffffu, ad, o);
+    }
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = aw; red[1][threadIdx.x >> 5] = ad; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double w = 0.0, d = 0.0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { w += red[0][i]; d += red[1][i]; }
+        gwet[0] = (float)w;
+        gdecay[0] = (float)d;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// block spectra.  Segment of block i holds samples n = (i-1)P + m, m = 0..2P-1.
+//   halves = 3: both halves (overlap-save input);  2: second half only ([0, g_i], adjoint of "keep last P");
+//   halves = 1 with block index i = j+1: first half only ([h_j, 0], an IR partition; single real signal).
+// reverse != 0 reads the signals back to front (for gx).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(CONV_THREADS) conv_spectra_kernel(const float* __restrict__ x, float2* __restrict__ S, int B,
+                                                                    int N, int nblk, int halves, int reverse, int blk_shift) {
+    extern __shared__ __align__(16) float2 fsm[];
+    float2* a = fsm;
+    float2* b = a + CONV_N2;
+    float2* tw = b + CONV_N2;
+    const int i = blockIdx.x, b2 = blockIdx.y, tid = threadIdx.x;
+    fft_fill_twiddles(tw, CONV_N2);
+    const int v0 = 2 * b2, v1 = 2 * b2 + 1;
+    const float* xa = x + (size_t)v0 * N;
+    const float* xb = v1 < B ? x + (size_t)v1 * N : nullptr;
+    const long long base = (long long)(i + blk_shift - 1) * CONV_P;
+    for (int m = tid; m < CONV_N2; m += CONV_THREADS) {
+        const bool on = (m < CONV_P) ? (halves & 1) : (halves & 2);
+        const long long n = base + m;
+        float re = 0.f, im = 0.f;
+        if (on && n >= 0 && n < N) {
+            const long long idx = reverse ? (N - 1 - n) : n;
+            re = xa[idx];
+            if (xb) im = xb[idx];
+        }
+        a[m] = make_float2(re, im);
+    }
+    __syncthreads();
+    const float2* out = block_fft<false>(a, b, tw, CONV_N2, tid, CONV_THREADS);
+    float2* dst = S + ((size_t)b2 * nblk + i) * CONV_N2;
+    for (int k = tid; k < CONV_N2; k += CONV_THREADS) dst[k] = out[k];
+}
+
+// y block i of voice pair b2: accumulate X[i-j]*H[j] over the IR partitions, inverse FFT, keep the last P.
+__global__ void __launch_bounds__(CONV_THREADS) conv_mac_ifft_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
+                                                                     float* __restrict__ y, int B, int N, int nblk, int np,
+                                                                     int reverse) {
+    extern __shared__ __align__(16) float2 fsm[];
+    float2* a = fsm;
+    float2* b = a + CONV_N2;
+    float2* tw = b + CONV_N2;
+    const int i = blockIdx.x, b2 = blockIdx.y, tid = threadIdx.x;
+    fft_fill_twiddles(tw, CONV_N2);
+    constexpr int PER = CONV_N2 / CONV_THREADS;
+    float2 acc[PER];
+#pragma unroll
+    for (int e = 0; e < PER; ++e) acc[e] = make_float2(0.f, 0.f);
+    const int jmax = i < np - 1 ? i : np - 1;
+    for (int j = 0; j <= jmax; ++j) {
+        const float2* xs = S + ((size_t)b2 * nblk + (i - j)) * CONV_N2;
+        const float2* hs = Hf + (size_t)j * CONV_N2;
+#pragma unroll
+        for (int e = 0; e < PER; ++e) {
+            const int k = tid + e * CONV_THREADS;
+            const float2 p = cmul(xs[k], hs[k]);
+            acc[e].x += p.x;
+            acc[e].y += p.y;
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < PER; ++e) a[tid + e * CONV_THREADS] = acc[e];
+    __syncthreads();
+    const float2* out = block_fft<true>(a, b, tw, CONV_N2, tid, CONV_THREADS);
+    const float scale = 1.0f / (float)CONV_N2;
+    const int v0 = 2 * b2, v1 = 2 * b2 + 1;
+    for (int m = tid; m < CONV_P; m += CONV_THREADS) {
+        const long long n = (long long)i * CONV_P + m;
+        if (n < N) {
+            const float2 v = out[CONV_P + m];
+            const long long idx = reverse ? (N - 1 - n) : n;
+            y[(size_t)v0 * N + idx] = v.x * scale;
+            if (v1 < B) y[(size_t)v1 * N + idx] = v.y * scale;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// gradient of the kernel:  gir[jP+q] = Re IFFT( sum_{b2,i} conj(X[b2,i-j]) * Gt[b2,i] )[q] / 4096,  q < P
+// Thread = frequency bin; CTA (bin tile, voice-pair chunk) walks its voice pairs and blocks, holding one
+// accumulator per IR partition.  Chunk partials are summed in a fixed order by the finish kernel.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
+                                                       float2* __restrict__ part, int B2, int nblk, int np, int jg) {
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    const int c = blockIdx.y;
+    const int per = (B2 + GIR_CHUNKS - 1) / GIR_CHUNKS;
+    const int b_lo = c * per, b_hi = min(B2, b_lo + per);
+    float2 acc[GIR_NP];
+#pragma unroll
+    for (int j = 0; j < GIR_NP; ++j) acc[j] = make_float2(0.f, 0.f);
+    for (int b2 = b_lo; b2 < b_hi; ++b2) {
+        const float2* xs = Xf + (size_t)b2 * nblk * CONV_N2 + k;
+        const float2* gs = Gf + (size_t)b2 * nblk * CONV_N2 + k;
+        for (int i = jg; i < nblk; ++i) {
+            const float2 g = gs[(size_t)i * CONV_N2];
+#pragma unroll
+            for (int j = 0; j < GIR_NP; ++j) {
+                const int src = i - jg - j;
+                if (jg + j < np && src >= 0) {
+                    const float2 xv = xs[(size_t)src * CONV_N2];
+                    const float2 p = cmul_conj(g, xv);            // g * conj(x)
+                    acc[j].x += p.x;
+                    acc[j].y += p.y;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < GIR_NP; ++j)
+        if (jg + j < np) part[((size_t)c * np + jg + j) * CONV_N2 + k] = acc[j];
+}
+
+__global__ void __launch_bounds__(CONV_THREADS) conv_gir_finish_kernel(const float2* __restrict__ part, float* __restrict__ gir,
+                                                                       int np, int Le) {
+    extern __shared__ __align__(16) float2 fsm[];
+    float2* a = fsm;
+    float2* b = a + CONV_N2;
+    float2* tw = b + CONV_N2;
+    const int j = blockIdx.x, tid = threadIdx.x;
+    fft_fill_twiddles(tw, CONV_N2);
+    for (int k = tid; k < CONV_N2; k += CONV_THREADS) {
+        float sx = 0.f, sy = 0.f;
+        for (int c = 0; c < GIR_CHUNKS; ++c) {
+            const float2 v = part[((size_t)c * np + j) * CONV_N2 + k];
+            sx += v.x;
+            sy += v.y;
+        }
+        a[k] = make_float2(sx, sy);
+    }
+    __syncthreads();
+    const float2* out = block_fft<true>(a, b, tw, CONV_N2, tid, CONV_THREADS);
+    const float scale = 1.0f / (float)CONV_N2;
+    for (int q = tid; q < CONV_P; q += CONV_THREADS) {
+        const int idx = j * CONV_P + q;
+        if (idx < Le) gir[idx] = out[q].x * scale;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// live_forward (reverb.py:40-49): slide the buffer, then only the last n outputs of the convolution
+// ------------------------------------------------------------------------------------------------
+__global__ void copy_kernel(const float* __restrict__ src, float* __restrict__ dst, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+}
+
+__global__ void __launch_bounds__(256) reverb_live_dot_kernel(const float* __restrict__ buf, const float* __restrict__ ir,
+                                                              float* __restrict__ y, int L, int n) {
+    __shared__ float red[8];
+    const int m = blockIdx.x;
+    const int p = L - n + m;                           // output position inside the buffer
+    float acc = 0.f;
+    for (int q = threadIdx.x; q <= p; q += 256) acc = fmaf(ir[q], buf[p - q], acc);
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float s = 0.f;
+        for (int w = 0; w < 8; ++w) s += red[w];
+        y[m] = s;
+    }
+}
+
+static int conv_smem_attr() {
+    static bool done = false;
+    const int bytes = (int)(sizeof(float2) * 3 * CONV_N2);
+    if (!done) {
+        cudaError_t e = cudaFuncSetAttribute(conv_spectra_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_mac_ifft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_gir_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        DDSP_REQUIRE(e == cudaSuccess, "conv: cannot reserve %d B of shared memory: %s", bytes, cudaGetErrorString(e));
+        done = true;
+    }
+    return 0;
+}
+
+static int check_conv(const char* fn, int B, int N, int Lk) {
+    DDSP_REQUIRE(B >= 1 && B <= 2 * 65535, "%s: B=%d out of range", fn, B);
+    DDSP_REQUIRE(N >= 1 && Lk >= 1, "%s: N=%d, Lk=%d must be positive", fn, N, Lk);
+    DDSP_REQUIRE((N + CONV_P - 1) / CONV_P <= 65535 * 32, "%s: N=%d too long", fn, N);
+    return 0;
+}
+
+}  // namespace ddsp
+
+using namespace ddsp;
+
+extern "C" int ddsp_reverb_impulse(const float* noise, const float* t, const float* decay, const float* wet, float* ir, int L,
+                                   void* stream) {
+    DDSP_REQUIRE(noise && t && decay && wet && ir && L >= 1, "ddsp_reverb_impulse: bad arguments");
+    reverb_impulse_kernel<<<(L + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(noise, t, decay, wet, ir, L);
+    DDSP_CHECK_LAUNCH("reverb_impulse_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_reverb_impulse_backward(const float* gir, const float* noise, const float* t, const float* decay,
+                                            const float* wet, float* gnoise, float* gdecay, float* gwet, int L, void* stream) {
+    DDSP_REQUIRE(gir && noise && t && decay && wet && gnoise && gdecay && gwet && L >= 1,
+                 "ddsp_reverb_impulse_backward: bad arguments");
+    reverb_impulse_bwd_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(gir, noise, t, decay, wet, gnoise, gdecay, gwet, L);
+    DDSP_CHECK_LAUNCH("reverb_impulse_bwd_kernel");
+    return 0;
+}
+
+extern "C" size_t ddsp_conv_scratch_bytes(int B, int N, int Lk) {
+    if (B < 1 || N < 1 || Lk < 1) return 0;
+    return conv_plan(B, N, Lk).total;
+}
+
+extern "C" int ddsp_conv_forward(const float* x, const float* ir, float* y, void* scratch, int B, int N, int Lk, void* stream) {
+    if (check_conv("ddsp_conv_forward", B, N, Lk)) return 1;
+    DDSP_REQUIRE(x && ir && y && scratch, "ddsp_conv_forward: null pointer argument");
+    if (conv_smem_attr()) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const ConvPlan p = conv_plan(B, N, Lk);
+    char* base = reinterpret_cast<char*>(scratch);
+    float2* Hf = reinterpret_cast<float2*>(base + p.off_H);
+    float2* S0 = reinterpret_cast<float2*>(base + p.off_S0);
+    const size_t smem = sizeof(float2) * 3 * CONV_N2;
+    const int Le = Lk < N ? Lk : N;
+    conv_spectra_kernel<<<dim3(p.np, 1), CONV_THREADS, smem, st>>>(ir, Hf, 1, Le, p.np, 1, 0, 1);
+    DDSP_CHECK_LAUNCH("conv_spectra_kernel(ir)");
+    conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(x, S0, B, N, p.nblk, 3, 0, 0);
+    DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
+    conv_mac_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S0, Hf, y, B, N, p.nblk, p.np, 0);
+    DDSP_CHECK_LAUNCH("conv_mac_ifft_kernel");
+    return 0;
+}
+
+extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* ir, float* gx, float* gir, void* scratch, int B,
+                                  int N, int Lk, void* stream) {
+    if (check_conv("ddsp_conv_backward", B, N, Lk)) return 1;
+    DDSP_REQUIRE(g && ir && scratch && (gx || gir) && (x || !gir), "ddsp_conv_backward: null pointer argument");
+    if (conv_smem_attr()) return 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const ConvPlan p = conv_plan(B, N, Lk);
+    char* base = reinterpret_cast<char*>(scratch);
+    float2* Hf = reinterpret_cast<float2*>(base + p.off_H);
+    float2* S0 = reinterpret_cast<float2*>(base + p.off_S0);
+    float2* S1 = reinterpret_cast<float2*>(base + p.off_S1);
+    float2* part = reinterpret_cast<float2*>(base + p.off_part);
+    const size_t smem = sizeof(float2) * 3 * CONV_N2;
+    const int Le = Lk < N ? Lk : N;
+    if (gx) {      // gx = flip(conv(flip(g), ir))
+        conv_spectra_kernel<<<dim3(p.np, 1), CONV_THREADS, smem, st>>>(ir, Hf, 1, Le, p.np, 1, 0, 1);
+        DDSP_CHECK_LAUNCH("conv_spectra_kernel(ir)");
+        conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S0, B, N, p.nblk, 3, 1, 0);
+        DDSP_CHECK_LAUNCH("conv_spectra_kernel(flip g)");
+        conv_mac_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S0, Hf, gx, B, N, p.nblk, p.np, 1);
+        DDSP_CHECK_LAUNCH("conv_mac_ifft_kernel(gx)");
+    }
+    if (gir) {
+        conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(x, S0, B, N, p.nblk, 3, 0, 0);
+        DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
+        conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S1, B, N, p.nblk, 2, 0, 0);
+        DDSP_CHECK_LAUNCH("conv_spectra_kernel(g tail)");
+        for (int jg = 0; jg < p.np; jg += GIR_NP) {
+            conv_gir_kernel<<<dim3(CONV_N2 / 256, GIR_CHUNKS), 256, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
+            DDSP_CHECK_LAUNCH("conv_gir_kernel");
+        }
+        cudaError_t e = cudaMemsetAsync(gir, 0, sizeof(float) * (size_t)Lk, st);
+        DDSP_REQUIRE(e == cudaSuccess, "ddsp_conv_backward: memset failed: %s", cudaGetErrorString(e));
+        conv_gir_finish_kernel<<<p.np, CONV_THREADS, smem, st>>>(part, gir, p.np, Le);
+        DDSP_CHECK_LAUNCH("conv_gir_finish_kernel");
+    }
+    return 0;
+}
+
+extern "C" int ddsp_reverb_live(float* buffer, const float* x, const float* ir, float* y, void* scratch, int L, int n,
+                                void* stream) {
+    DDSP_REQUIRE(buffer && x && ir && y && scratch, "ddsp_reverb_live: null pointer argument");
+    DDSP_REQUIRE(L >= 1 && n >= 1 && n <= L, "ddsp_reverb_live: need 1 <= n <= L (n=%d, L=%d)", n, L);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    float* tmp = reinterpret_cast<float*>(scratch);    // >= L floats
+    if (L - n > 0) {
+        copy_kernel<<<(L - n + 255) / 256, 256, 0, st>>>(buffer + n, tmp, L - n);
+        copy_kernel<<<(L - n + 255) / 256, 256, 0, st>>>(tmp, buffer, L - n);
+    }
+    copy_kernel<<<(n + 255) / 256, 256, 0, st>>>(x, buffer + (L - n), n);
+    reverb_live_dot_kernel<<<n, 256, 0, st>>>(buffer, ir, y, L, n);
+    DDSP_CHECK_LAUNCH("reverb_live kernels");
+    return 0;
+}

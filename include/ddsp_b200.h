@@ -97,6 +97,57 @@ int ddsp_noise_uniform(float* out, uint64_t seed, uint32_t offset, uint32_t voic
 int ddsp_amp_to_impulse_response(const float* H, float* ir, int R, int NB, int target, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Reverb  --  reverb.py
+ * ------------------------------------------------------------------------------------------ */
+
+/* Reverb.build_impulse, reverb.py:24-29: ir[L] = noise*exp(-softplus(-decay)*t*500)*sigmoid(wet), ir[0]=1.
+ * noise [L], t [L], decay/wet: device scalars. */
+int ddsp_reverb_impulse(const float* noise, const float* t, const float* decay, const float* wet,
+                        float* ir, int L, void* stream);
+
+/* Backward of build_impulse: gir [L] -> gnoise [L], gdecay [1], gwet [1]. */
+int ddsp_reverb_impulse_backward(const float* gir, const float* noise, const float* t,
+                                 const float* decay, const float* wet, float* gnoise, float* gdecay,
+                                 float* gwet, int L, void* stream);
+
+/* fft_convolve with a shared kernel, filtered_noise.py:25-32 as used by Reverb.forward reverb.py:31-38:
+ * y[b,n] = sum_{m<=n, m<Lk} ir[m] * x[b,n-m], n < N   (ir is cropped to N when Lk > N).
+ * scratch: ddsp_conv_scratch_bytes(B, N, Lk). */
+size_t ddsp_conv_scratch_bytes(int B, int N, int Lk);
+int ddsp_conv_forward(const float* x, const float* ir, float* y, void* scratch, int B, int N, int Lk,
+                      void* stream);
+/* gx[b,m] = sum_{n>=m} g[b,n]*ir[n-m];  gir[q] = sum_b sum_{n>=q} g[b,n]*x[b,n-q]. Either output may be NULL. */
+int ddsp_conv_backward(const float* g, const float* x, const float* ir, float* gx, float* gir,
+                       void* scratch, int B, int N, int Lk, void* stream);
+
+/* Reverb.live_forward, reverb.py:40-49: buffer[L] <- shift left by n, append x[n]; y[n] = last n
+ * samples of causal_conv(buffer, ir). */
+int ddsp_reverb_live(float* buffer, const float* x, const float* ir, float* y, void* scratch, int L,
+                     int n, void* stream);   /* scratch: >= L floats */
+
+/* ------------------------------------------------------------------------------------------
+ * Multi-scale spectral loss  --  loss/mss_loss.py:11-68 (torchaudio Spectrogram defaults: power
+ * spectrogram, periodic Hann, center reflect pad, onesided; hop = int(n_fft*(1-overlap))).
+ * ------------------------------------------------------------------------------------------ */
+
+/* Elements of one scale's spectrogram: B * (n_fft/2+1) * (1 + N/hop)  (the `mean` denominators of :29-30). */
+int64_t ddsp_mss_count(int B, int N, int n_fft, int hop);
+
+/* MSSLoss.forward, mss_loss.py:57-68.  x_pred, x_true [B,N].
+ *   loss_terms (device, double[1 + 2*n_scales], zeroed here): [0] the loss
+ *     sum_s ( sum|Sp-St| + alpha*sum|log2(St+eps)-log2(Sp+eps)| ) / count_s, then per scale the two raw sums;
+ *   loss_f32 (device float[1]) or NULL: the loss rounded to fp32;
+ *   gx [B,N] or NULL (zeroed here): d loss / d x_pred, produced in the same pass.
+ *   n_ffts_host / hops_host: HOST int arrays; n_fft a power of two in [4,4096], n_fft/2 < N. */
+int ddsp_mss_forward(const float* x_pred, const float* x_true, double* loss_terms, float* loss_f32,
+                     float* gx, const int* n_ffts_host, const int* hops_host, int n_scales, float alpha,
+                     float eps, int B, int N, void* stream);
+
+/* Backward of the scalar loss: gx_out = gloss[0] * gx_saved   (gloss: device float scalar). */
+int ddsp_mss_backward(const float* gloss, const float* gx_saved, float* gx_out, int B, int N,
+                      void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Measurement helper: dependent-free FFMA chains, for the measured FP32 roofline denominator.
  * Each thread executes iters*64 FFMAs; out[grid*block] keeps the compiler honest.
  * ------------------------------------------------------------------------------------------ */
