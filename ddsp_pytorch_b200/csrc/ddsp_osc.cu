@@ -510,3 +510,72 @@ extern "C" int ddsp_osc_backward(const float* g, const float* f0, const float* a
     if (rc) return rc;
     return ddsp_osc_grad_finalize(f0, state, scratch, gc, ga, B, T, K, hop, sample_rate, stream);
 }
+
+// ------------------------------------------------------------------------------------------------
+// streaming variant -- OscillatorBank.live (harmonic_oscillator.py:64-75)
+// Voice 0 starts every harmonic from its own carried phase last[k] (radians), so harmonic k has phase
+// last[k] + 2 pi k Theta and the single-seed recurrence does not apply; blocks are a few thousand samples,
+// so each harmonic-sample is evaluated directly (fp64 phase, sinpi).  Launch-latency bound by nature.
+// ------------------------------------------------------------------------------------------------
+namespace ddsp {
+
+__global__ void __launch_bounds__(256) osc_live_kernel(const float* __restrict__ cn, const float* __restrict__ a,
+                                                       const float* __restrict__ f0, const int* __restrict__ kact,
+                                                       const double* __restrict__ phase0, const float* __restrict__ last_in,
+                                                       float* __restrict__ y, int T, int K, int hop, double inv_sr) {
+    const int s = blockIdx.x, b = blockIdx.y;
+    const Segment g = make_segment(s, T, hop, f0 + (size_t)b * T, phase0 + (size_t)b * (T + 1), inv_sr);
+    const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
+    const int kmax = max(kact[fL], kact[fR]);
+    const float* cl = cn + fL * K;
+    const float* cr = cn + fR * K;
+    const float aL = a[fL], da = a[fR] - aL;
+    const double inv_2pi = 0.15915494309189533577;
+    for (int r = g.r_lo + threadIdx.x; r < g.r_hi; r += blockDim.x) {
+        const double rr = (double)(r + 1);
+        const double theta = fma(g.du * rr, rr, fma(rr, g.uL, g.E));        // cycles, not wrapped
+        const float w = ((float)r + 0.5f) / (float)hop;
+        float acc = 0.f;
+        for (int k = 0; k < kmax; ++k) {
+            double ph = theta * (double)(k + 1);
+            if (b == 0) ph += (double)last_in[k] * inv_2pi;
+            ph -= rint(ph);
+            const float amp = fmaf(w, cr[k] - cl[k], cl[k]);
+            acc = fmaf(amp, sinpif(2.0f * (float)ph), acc);
+        }
+        y[(size_t)b * T * hop + (g.n0 + r)] = fmaf(w, da, aL) * acc;
+    }
+}
+
+// new carried phases: wrapped phase of voice 0's last sample (:72)
+__global__ void osc_live_state_kernel(const float* __restrict__ f0, const double* __restrict__ phase0,
+                                      const float* __restrict__ last_in, float* __restrict__ last_out, int T, int K, int hop,
+                                      double inv_sr) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    const Segment g = make_segment(T, T, hop, f0, phase0, inv_sr);
+    const double rr = (double)(hop / 2);                                     // r = hop/2 - 1 is the last sample
+    const double theta = fma(g.du * rr, rr, fma(rr, g.uL, g.E));
+    double ph = theta * (double)(k + 1) + (double)last_in[k] * 0.15915494309189533577;
+    ph -= floor(ph);
+    last_out[k] = (float)(ph * 6.283185307179586476925);
+}
+
+}  // namespace ddsp
+
+extern "C" int ddsp_osc_live(const float* f0, const float* c, const float* a, const float* last_in, float* last_out, float* y,
+                             void* state, int B, int T, int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_live", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(f0 && c && a && last_in && last_out && y && state, "ddsp_osc_live: null pointer argument");
+    DDSP_REQUIRE(last_in != last_out, "ddsp_osc_live: last_in and last_out must not alias");
+    int rc = ddsp_osc_prepare(f0, c, state, B, T, K, hop, sample_rate, stream);
+    if (rc) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const OscState S = carve_osc_state(state, B, T, K);
+    const double inv_sr = 1.0 / (double)sample_rate;
+    osc_live_kernel<<<dim3(T + 1, B), 256, 0, st>>>(S.cn, a, f0, S.kact, S.phase0, last_in, y, T, K, hop, inv_sr);
+    DDSP_CHECK_LAUNCH("osc_live_kernel");
+    osc_live_state_kernel<<<(K + 127) / 128, 128, 0, st>>>(f0, S.phase0, last_in, last_out, T, K, hop, inv_sr);
+    DDSP_CHECK_LAUNCH("osc_live_state_kernel");
+    return 0;
+}

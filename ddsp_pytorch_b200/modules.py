@@ -47,3 +47,91 @@ class FilteredNoise(nn.Module):
         offset = self.calls
         self.calls += 1
         return ops.filtered_noise(x["H"], self.block_size, self.seed, offset, self.voice_offset, noise=noise)
+
+
+def _live(self, x):
+    """OscillatorBank.live (harmonic_oscillator.py:64-75): carries per-harmonic phases across calls (voice 0)."""
+    y, new_last = ops.oscillator_live(x["f0"], x["c"], x["a"], self.last_phases.data, self.sample_rate, self.hop_size)
+    self.last_phases.data = new_last            # int64 zeros before the first call, fp32 afterwards -- as the reference
+    return y
+
+
+OscillatorBank.live = _live
+
+
+def fft_convolve(signal: torch.Tensor, kernel: torch.Tensor) -> torch.Tensor:
+    """filtered_noise.py:25-32 for the shapes the reference uses it with a shared kernel: signal [B,n], kernel [1,n]."""
+    if signal.dim() != 2 or kernel.numel() != kernel.shape[-1]:
+        raise RuntimeError("fft_convolve: this build supports signal [B,n] with one shared kernel [1,n]")
+    return ops.causal_conv(signal, kernel)
+
+
+amp_to_impulse_response = ops.amp_to_impulse_response
+
+
+class Reverb(nn.Module):
+    """Drop-in for model/ddsp/reverb.py:8-49 (same parameters, buffers-as-Parameters and state-dict keys)."""
+
+    def __init__(self, conf, initial_wet=0, initial_decay=5):
+        super().__init__()
+        self.length = conf.sample_rate
+        self.sampling_rate = conf.sample_rate
+        self.noise = nn.Parameter(torch.rand(self.length) * 2 - 1)
+        self.decay = nn.Parameter(torch.tensor(float(initial_decay)))
+        self.wet = nn.Parameter(torch.tensor(float(initial_wet)))
+        t = (torch.arange(self.length) / self.sampling_rate).reshape(1, -1)
+        self.t = nn.Parameter(t, requires_grad=False)
+        self.buffer = nn.Parameter(torch.zeros(1, self.length), requires_grad=False)
+
+    def build_impulse(self):
+        return ops.reverb_impulse(self.noise, self.decay, self.wet, self.t)
+
+    def forward(self, x):
+        # reverb.py:34 pads (or crops) the impulse to len(x); taps at lags >= len(x) cannot reach an output,
+        # so the kernel takes the impulse as it is
+        return ops.causal_conv(x, self.build_impulse())
+
+    def live_forward(self, x):
+        with torch.no_grad():
+            return ops.reverb_live(self.buffer.data, x, self.build_impulse())
+
+
+class _HannWindowHolder(nn.Module):
+    """Keeps the ``stft.window`` buffer of torchaudio's Spectrogram in the state dict (mss_loss.py:23)."""
+
+    def __init__(self, n_fft):
+        super().__init__()
+        self.register_buffer("window", torch.hann_window(n_fft))
+
+
+class SSSLoss(nn.Module):
+    """Drop-in for loss/mss_loss.py:11-33."""
+
+    def __init__(self, n_fft, alpha=1.0, overlap=0.75, eps=1e-7):
+        super().__init__()
+        self.n_fft = n_fft
+        self.alpha = alpha
+        self.eps = eps
+        self.overlap = overlap
+        self.hop_length = int(n_fft * (1 - overlap))
+        self.stft = _HannWindowHolder(n_fft)
+
+    def forward(self, x_pred, x_true):
+        return ops.mss_loss(x_pred, x_true, [self.n_fft], self.alpha, self.overlap, self.eps)
+
+
+class MSSLoss(nn.Module):
+    """Drop-in for loss/mss_loss.py:36-68: all scales are evaluated by one call into the library."""
+
+    def __init__(self, n_ffts: list, alpha=1.0, overlap=0.75, eps=1e-7, use_reverb=True):
+        super().__init__()
+        self.losses = nn.ModuleList([SSSLoss(n_fft, alpha, overlap, eps) for n_fft in n_ffts])
+        self.n_ffts, self.alpha, self.overlap, self.eps = list(n_ffts), alpha, overlap, eps
+        self.signal_key = "audio_reverb" if use_reverb else "audio_synth"
+
+    def forward(self, x_pred, x_true):
+        if isinstance(x_pred, dict):
+            x_pred = x_pred[self.signal_key]
+        if isinstance(x_true, dict):
+            x_true = x_true["audio"]
+        return ops.mss_loss(x_pred, x_true, self.n_ffts, self.alpha, self.overlap, self.eps)

@@ -155,3 +155,151 @@ def probe_fp32_fma_tflops(iters: int = 4096, reps: int = 5) -> float:
         flops = 2.0 * 64 * iters * blocks * threads
         best = max(best, flops / (e0.elapsed_time(e1) * 1e-3) / 1e12)
     return best
+
+
+# ------------------------------------------------------------------------------------------------------
+# Reverb
+# ------------------------------------------------------------------------------------------------------
+class _ReverbImpulse(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, noise, decay, wet, t):
+        n_, d_, w_, t_ = _f32(noise).view(-1), _f32(decay).view(1), _f32(wet).view(1), _f32(t).view(-1)
+        L = n_.numel()
+        ir = torch.empty(1, L, dtype=torch.float32, device=n_.device)
+        with torch.cuda.device(n_.device):
+            _lib.call("ddsp_reverb_impulse", n_.data_ptr(), t_.data_ptr(), d_.data_ptr(), w_.data_ptr(), ir.data_ptr(), L, _stream())
+        ctx.save_for_backward(n_, d_, w_, t_)
+        ctx.meta = (noise.shape, decay.shape, wet.shape)
+        return ir
+
+    @staticmethod
+    def backward(ctx, gir):
+        n_, d_, w_, t_ = ctx.saved_tensors
+        L = n_.numel()
+        g_ = _f32(gir).view(-1)
+        gn = torch.empty(L, dtype=torch.float32, device=n_.device)
+        gd = torch.empty(1, dtype=torch.float32, device=n_.device)
+        gw = torch.empty(1, dtype=torch.float32, device=n_.device)
+        with torch.cuda.device(n_.device):
+            _lib.call("ddsp_reverb_impulse_backward", g_.data_ptr(), n_.data_ptr(), t_.data_ptr(), d_.data_ptr(), w_.data_ptr(),
+                      gn.data_ptr(), gd.data_ptr(), gw.data_ptr(), L, _stream())
+        ns, ds, ws = ctx.meta
+        return gn.view(ns), gd.view(ds), gw.view(ws), None
+
+
+def reverb_impulse(noise, decay, wet, t) -> torch.Tensor:
+    """Reverb.build_impulse (reverb.py:24-29): -> [1,L]."""
+    return _ReverbImpulse.apply(noise, decay, wet, t)
+
+
+class _CausalConv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, ir):
+        x_, ir_ = _f32(x), _f32(ir).view(-1)
+        B, N = x_.shape
+        Lk = ir_.numel()
+        y = torch.empty(B, N, dtype=torch.float32, device=x_.device)
+        with torch.cuda.device(x_.device):
+            scratch = _bytes(_lib.load().ddsp_conv_scratch_bytes(B, N, Lk), x_.device)
+            _lib.call("ddsp_conv_forward", x_.data_ptr(), ir_.data_ptr(), y.data_ptr(), scratch.data_ptr(), B, N, Lk, _stream())
+        ctx.save_for_backward(x_, ir_)
+        ctx.meta = (x.dtype, ir.shape, ir.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x_, ir_ = ctx.saved_tensors
+        B, N = x_.shape
+        Lk = ir_.numel()
+        g_ = _f32(g)
+        need_x, need_ir = ctx.needs_input_grad
+        gx = torch.empty(B, N, dtype=torch.float32, device=x_.device) if need_x else None
+        gir = torch.empty(Lk, dtype=torch.float32, device=x_.device) if need_ir else None
+        with torch.cuda.device(x_.device):
+            scratch = _bytes(_lib.load().ddsp_conv_scratch_bytes(B, N, Lk), x_.device)
+            _lib.call("ddsp_conv_backward", g_.data_ptr(), x_.data_ptr(), ir_.data_ptr(),
+                      gx.data_ptr() if need_x else None, gir.data_ptr() if need_ir else None, scratch.data_ptr(), B, N, Lk,
+                      _stream())
+        xd, irs, ird = ctx.meta
+        return (gx.to(xd) if need_x else None), (gir.view(irs).to(ird) if need_ir else None)
+
+
+def causal_conv(x: torch.Tensor, ir: torch.Tensor) -> torch.Tensor:
+    """x [B,N], ir [1,Lk] or [Lk] shared by the batch -> y[b,n] = sum_{q<=n} ir[q] x[b,n-q]
+    (fft_convolve as Reverb.forward uses it, reverb.py:31-38; taps at lags >= N are irrelevant, so the
+    reference's crop/pad of the IR to N is implicit)."""
+    return _CausalConv.apply(x, ir)
+
+
+def reverb_live(buffer: torch.Tensor, x: torch.Tensor, ir: torch.Tensor) -> torch.Tensor:
+    """Reverb.live_forward (reverb.py:40-49): updates ``buffer`` [1,L] in place, returns the last len(x) outputs [1,n]."""
+    x_, ir_ = _f32(x).view(-1), _f32(ir).view(-1)
+    L, n = buffer.numel(), x_.numel()
+    if buffer.dtype != torch.float32 or not buffer.is_cuda or not buffer.is_contiguous():
+        raise RuntimeError("reverb_live: buffer must be a contiguous fp32 CUDA tensor")
+    y = torch.empty(1, n, dtype=torch.float32, device=buffer.device)
+    with torch.cuda.device(buffer.device):
+        scratch = torch.empty(L, dtype=torch.float32, device=buffer.device)
+        _lib.call("ddsp_reverb_live", buffer.data_ptr(), x_.data_ptr(), ir_.data_ptr(), y.data_ptr(), scratch.data_ptr(), L, n,
+                  _stream())
+    return y
+
+
+# ------------------------------------------------------------------------------------------------------
+# Multi-scale spectral loss
+# ------------------------------------------------------------------------------------------------------
+class _MSSLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_pred, x_true, n_ffts, hops, alpha: float, eps: float):
+        import ctypes as C
+        xp, xt = _f32(x_pred), _f32(x_true)
+        if xp.dim() != 2 or xp.shape != xt.shape:
+            raise RuntimeError(f"mss_loss: x_pred {tuple(x_pred.shape)} and x_true {tuple(x_true.shape)} must both be [B,N]")
+        B, N = xp.shape
+        ns = len(n_ffts)
+        dev = xp.device
+        need_grad = x_pred.requires_grad
+        terms = torch.empty(1 + 2 * ns, dtype=torch.float64, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        gx = torch.empty(B, N, dtype=torch.float32, device=dev) if need_grad else None
+        nf = (C.c_int * ns)(*[int(v) for v in n_ffts])
+        hp = (C.c_int * ns)(*[int(v) for v in hops])
+        with torch.cuda.device(dev):
+            _lib.call("ddsp_mss_forward", xp.data_ptr(), xt.data_ptr(), terms.data_ptr(), loss.data_ptr(),
+                      gx.data_ptr() if need_grad else None, C.cast(nf, C.c_void_p), C.cast(hp, C.c_void_p), ns, float(alpha),
+                      float(eps), B, N, _stream())
+        if need_grad:
+            ctx.save_for_backward(gx)
+        ctx.meta = (x_pred.dtype, B, N)
+        ctx.terms = terms
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        (gx,) = ctx.saved_tensors
+        dt, B, N = ctx.meta
+        gl = _f32(gloss).view(1)
+        out = torch.empty_like(gx)
+        with torch.cuda.device(gx.device):
+            _lib.call("ddsp_mss_backward", gl.data_ptr(), gx.data_ptr(), out.data_ptr(), B, N, _stream())
+        return out.to(dt), None, None, None, None, None
+
+
+def mss_loss(x_pred, x_true, n_ffts, alpha: float = 1.0, overlap: float = 0.75, eps: float = 1e-7) -> torch.Tensor:
+    """MSSLoss.forward (mss_loss.py:57-68) on tensors [B,N] -> 0-dim fp32 loss; gradient flows to x_pred only."""
+    hops = [int(n * (1 - overlap)) for n in n_ffts]          # mss_loss.py:21
+    return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps))
+
+
+def oscillator_live(f0, c, a, last_phases, sample_rate: int, hop: int):
+    """OscillatorBank.live (harmonic_oscillator.py:64-75), no gradient: returns (audio [B,T*hop], new last_phases [K] fp32)."""
+    f0_, c_, a_ = _f32(f0), _f32(c), _f32(a)
+    B, T, K = c_.shape
+    last_in = last_phases.detach().to(device=c_.device, dtype=torch.float32).contiguous()
+    last_out = torch.empty(K, dtype=torch.float32, device=c_.device)
+    y = torch.empty(B, T * hop, dtype=torch.float32, device=c_.device)
+    with torch.cuda.device(c_.device):
+        state = _bytes(_lib.load().ddsp_osc_state_bytes(B, T, K), c_.device)
+        _lib.call("ddsp_osc_live", f0_.data_ptr(), c_.data_ptr(), a_.data_ptr(), last_in.data_ptr(), last_out.data_ptr(),
+                  y.data_ptr(), state.data_ptr(), B, T, K, int(hop), int(sample_rate), _stream())
+    return y, last_out

@@ -71,6 +71,13 @@ int ddsp_osc_grad_segments(const float* g, const float* f0, const float* a, cons
 int ddsp_osc_grad_finalize(const float* f0, const void* state, const void* scratch, float* gc,
                            float* ga, int B, int T, int K, int hop, int sample_rate, void* stream);
 
+/* OscillatorBank.live, harmonic_oscillator.py:64-75: as forward, but voice 0 starts harmonic k from the
+ * carried phase last_in[k] (radians; arbitrary per-harmonic values are honoured) and last_out[k] receives
+ * the wrapped phase of voice 0's last sample (:72).  last_in and last_out must not alias. */
+int ddsp_osc_live(const float* f0, const float* c, const float* a, const float* last_in,
+                  float* last_out, float* y, void* state, int B, int T, int K, int hop,
+                  int sample_rate, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Filtered noise  --  FilteredNoise.forward, filtered_noise.py:40-53
  *   (amp_to_impulse_response :7-22, fft_convolve :25-32; per frame, tails dropped, no overlap-add)

@@ -1,0 +1,147 @@
+"""Parity of the CUDA reverb, spectral loss and streaming paths with the reference's fp64 outputs (golden
+fixtures) and with the oracle.  Tolerances per SURVEY.md §8c: reverb <= 1e-4 of max|y|; MSS loss and all
+gradients <= 1e-4 relative (norm-wise)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def rel(got, want):
+    want = torch.as_tensor(want).double()
+    return float((got.detach().double().cpu() - want).abs().max() / want.abs().max().clamp_min(1e-30))
+
+
+def cu(x, grad=False):
+    return torch.as_tensor(np.asarray(x), dtype=torch.float32).cuda().requires_grad_(grad)
+
+
+@pytest.mark.parametrize("name", ["ref_reverb_long.npz", "ref_reverb_crop.npz"])
+def test_reverb_golden(golden, name):
+    from ddsp_pytorch_b200 import ops
+    g = golden(name)
+    noise, x = cu(g["noise"], True), cu(g["x"], True)
+    decay, wet = cu(g["decay"], True), cu(g["wet"], True)
+    ir = ops.reverb_impulse(noise, decay, wet, cu(g["t"]))
+    assert rel(ir, g["ir64"]) <= 1e-6
+    y = ops.causal_conv(x, ir)
+    assert rel(y, g["y64"]) <= TOL
+    (y * cu(g["gup"])).sum().backward()
+    assert rel(x.grad, g["gx"]) <= TOL
+    assert rel(noise.grad, g["gnoise"]) <= TOL
+    assert abs(float(decay.grad) - float(g["gdecay"])) <= TOL * abs(float(g["gdecay"]))
+    assert abs(float(wet.grad) - float(g["gwet"])) <= TOL * abs(float(g["gwet"]))
+
+
+@pytest.mark.parametrize("B,N,L", [(3, 9000, 5000), (2, 4096, 4096), (1, 2048, 44100), (5, 20000, 16000), (2, 6000, 2049),
+                                   (1, 100, 7)])
+def test_conv_against_oracle(B, N, L):
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(N + L)
+    x = torch.randn(B, N, generator=gen) * 0.3
+    ir = torch.randn(1, L, generator=gen) * torch.exp(-torch.arange(L) / (0.2 * L))
+    gup = torch.randn(B, N, generator=gen)
+    xd, ird = x.double().requires_grad_(True), ir.double().requires_grad_(True)
+    want = O.reverb_apply(xd, ird)
+    (want * gup.double()).sum().backward()
+    xc, irc = x.cuda().requires_grad_(True), ir.cuda().requires_grad_(True)
+    y = ops.causal_conv(xc, irc)
+    (y * gup.cuda()).sum().backward()
+    assert rel(y, want.detach()) <= TOL
+    assert rel(xc.grad, xd.grad) <= TOL
+    assert rel(irc.grad, ird.grad) <= TOL
+
+
+def test_reverb_module_forward_and_live(golden):
+    import ddsp_pytorch_b200 as d
+    g = golden("ref_reverb_live.npz")
+    sr = int(g["sr"])
+    rv = d.Reverb(d.Config(sample_rate=sr), initial_wet=float(g["wet"]), initial_decay=float(g["decay"])).cuda()
+    rv.noise.data = cu(g["noise"])
+    assert set(rv.state_dict()) == {"noise", "decay", "wet", "t", "buffer"}
+    for i in range(int(g["calls"])):
+        y = rv.live_forward(cu(g[f"x_{i}"]))
+        assert rel(y, g[f"y64_{i}"]) <= TOL
+        assert float((rv.buffer.double().cpu() - torch.from_numpy(g[f"buf64_{i}"])).abs().max()) < 1e-7
+
+
+def test_mss_golden(golden):
+    from ddsp_pytorch_b200 import ops
+    import ddsp_pytorch_b200 as d
+    g = golden("ref_mss.npz")
+    n_ffts = [int(n) for n in g["n_ffts"]]
+    xp, xt = cu(g["x_pred"], True), cu(g["x_true"])
+    loss = d.MSSLoss(n_ffts).cuda()(xp, xt)
+    assert loss.dim() == 0 and loss.dtype == torch.float32
+    assert abs(float(loss) - float(g["loss64"])) <= TOL * float(g["loss64"])
+    loss.backward()
+    assert rel(xp.grad, g["gx"]) <= TOL
+    for n, want in zip(n_ffts, g["per_scale64"]):
+        assert abs(float(ops.mss_loss(xp.detach(), xt, [n])) - float(want)) <= TOL * float(want)
+
+
+@pytest.mark.parametrize("B,N,n_ffts", [(3, 5000, [64, 128, 256]), (1, 2050, [4096, 2048]), (2, 777, [16, 32, 8]),
+                                        (4, 64000, [2048, 1024, 512, 256, 128, 64])])
+def test_mss_against_oracle(B, N, n_ffts):
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(N)
+    xt = (torch.randn(B, N, generator=gen) * 0.1).clamp(-1, 1)
+    xp = 0.5 * xt + torch.randn(B, N, generator=gen) * 0.05
+    xpd = xp.double().requires_grad_(True)
+    want = O.mss_loss(xpd, xt.double(), n_ffts)
+    (want * 0.7).backward()
+    xpc = xp.cuda().requires_grad_(True)
+    got = ops.mss_loss(xpc, xt.cuda(), n_ffts)
+    (got * 0.7).backward()
+    assert abs(float(got) - float(want)) <= TOL * float(want)
+    assert rel(xpc.grad, xpd.grad) <= TOL
+
+
+def test_mss_dict_inputs_and_identity():
+    import ddsp_pytorch_b200 as d
+    x = torch.randn(2, 4096).cuda() * 0.1
+    m = d.MSSLoss([256, 64])
+    assert float(m({"audio_reverb": x, "hidden": None}, {"audio": x})) == 0.0
+
+
+def test_osc_live_golden(golden):
+    import ddsp_pytorch_b200 as d
+    g = golden("ref_osc_live.npz")
+    K, sr, hop = int(g["K"]), int(g["sr"]), int(g["hop"])
+    bank = d.OscillatorBank(d.Config(n_harmonics=K, sample_rate=sr, hop_length=hop)).cuda()
+    assert bank.last_phases.dtype == torch.int64
+    for i in range(int(g["calls"])):
+        y = bank.live({"f0": cu(g[f"f0_{i}"]), "c": cu(g[f"c_{i}"]), "a": cu(g[f"a_{i}"])})
+        assert float((y.double().cpu() - torch.from_numpy(g[f"y64_{i}"])).abs().max()) <= TOL
+        dphi = (bank.last_phases.double().cpu() - torch.from_numpy(g[f"phase64_{i}"])).abs()
+        assert float(torch.minimum(dphi, 2 * np.pi - dphi).max()) <= 1e-4
+    assert bank.last_phases.dtype == torch.float32
+    # rt-length clip: also within 1e-3 of the fp32 reference
+    assert float((y.cpu() - torch.from_numpy(g[f"y32_{int(g['calls']) - 1}"])).abs().max()) <= 1e-3
+
+
+def test_whole_path_golden(golden):
+    """harmonics + noise -> reverb -> MSS with gradients to every trainable input (decoder.py:129-133, train.py:33-34)."""
+    import ddsp_pytorch_b200 as d
+    g = golden("ref_path.npz")
+    K, NB, sr, hop = int(g["K"]), int(g["NB"]), int(g["sr"]), int(g["hop"])
+    conf = d.Config(n_harmonics=K, n_noise_filters=NB, sample_rate=sr, hop_length=hop)
+    bank, fn, rv = d.OscillatorBank(conf).cuda(), d.FilteredNoise(conf), d.Reverb(conf, float(g["rev_wet"]), float(g["rev_decay"])).cuda()
+    rv.noise.data = cu(g["rev_noise"])
+    c, a, H = cu(g["c"], True), cu(g["a"], True), cu(g["H"], True)
+    ctrl = {"f0": cu(g["f0"]), "c": c, "a": a, "H": H}
+    dry = bank(ctrl) + fn(ctrl, noise=cu(g["noise"]))
+    assert rel(dry, g["dry64"]) <= TOL
+    y = rv(dry)
+    assert rel(y, g["y64"]) <= TOL
+    loss = d.MSSLoss([int(n) for n in g["n_ffts"]])(y, cu(g["target"]))
+    assert abs(float(loss) - float(g["loss64"])) <= TOL * float(g["loss64"])
+    loss.backward()
+    for got, key in ((c.grad, "gc"), (a.grad, "ga"), (H.grad, "gH"), (rv.noise.grad, "g_rev_noise")):
+        assert rel(got, g[key]) <= 2e-4, key
+    assert abs(float(rv.decay.grad) - float(g["g_rev_decay"])) <= 2e-4 * abs(float(g["g_rev_decay"]))
+    assert abs(float(rv.wet.grad) - float(g["g_rev_wet"])) <= 2e-4 * abs(float(g["g_rev_wet"]))
