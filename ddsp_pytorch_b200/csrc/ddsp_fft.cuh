@@ -4,8 +4,8 @@
 // reference calls cuFFT through torch.fft / torch.stft.
 //
 //   * data: float2[n] ping-pong pair in shared memory, natural order in, natural order out;
-//   * twiddles: float2 tw[n] in shared memory, tw[q] = (cos(2 pi q/n), -sin(2 pi q/n)), filled once per
-//     CTA by fft_fill_twiddles (sincospif on an exactly representable argument: <= 1 ulp);
+//   * twiddles: float2 tw[n] in shared memory, tw[q] = (cos(2 pi q/n), -sin(2 pi q/n)), copied once per CTA
+//     from a device table rounded from fp64 (fft_ensure_table must have run on the host side);
 //   * a "group" of `gsize` threads (any divisor layout of the CTA) owns one transform; every pass ends
 //     with a CTA-wide __syncthreads(), so all groups of a CTA must transform the same n together.
 #pragma once
@@ -22,13 +22,39 @@ __device__ __forceinline__ float2 cmul_conj(float2 a, float2 b) {   // a * conj(
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 
-__device__ __forceinline__ void fft_fill_twiddles(float2* tw, int n) {
-    const float inv = 2.0f / (float)n;
-    for (int q = threadIdx.x; q < n; q += blockDim.x) {
-        float s, c;
-        sincospif((float)q * inv, &s, &c);
-        tw[q] = make_float2(c, -s);
+// Twiddle table for the largest transform (4096), rounded from fp64: tw[q] = (cos, -sin)(2 pi q / 4096).
+// Exactly rounded twiddles keep the fp32 transform at the accuracy of a CPU fp32 FFT (rel. error 1.1e-7 at
+// n = 2048; 1-ulp sincospif twiddles measured 2.0e-7), which the spectral-loss gradient is sensitive to.
+// Each translation unit owns a copy, filled once per device by the first call that needs it.
+constexpr int FFT_MAX = 4096;
+static __device__ float2 g_fft_tw[FFT_MAX];
+
+static __global__ void fft_init_table_kernel() {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q < FFT_MAX) {
+        double sn, cs;
+        sincospi(2.0 * (double)q / (double)FFT_MAX, &sn, &cs);
+        g_fft_tw[q] = make_float2((float)cs, (float)-sn);
     }
+}
+
+static inline cudaError_t fft_ensure_table(cudaStream_t st) {
+    static bool done[64] = {false};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || !done[dev]) {
+        fft_init_table_kernel<<<FFT_MAX / 256, 256, 0, st>>>();
+        e = cudaStreamSynchronize(st);                  // one-time: later calls on other streams see the table
+        if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;
+    }
+    return e;
+}
+
+// copy the stride-(4096/n) subset of the table into shared memory: tw[q] = exp(-2 pi i q / n)
+__device__ __forceinline__ void fft_fill_twiddles(float2* tw, int n) {
+    const int stride = FFT_MAX / n;
+    for (int q = threadIdx.x; q < n; q += blockDim.x) tw[q] = g_fft_tw[q * stride];
 }
 
 // One transform of size n by the `gsize` threads gtid = 0..gsize-1.  `a` holds the input; returns the buffer

@@ -4,10 +4,11 @@
 // cuFFT + abs().pow(2)) and then ~8 elementwise / reduction passes over a 2-4x oversampled spectrogram,
 // and autograd replays all of it backwards.  Here one kernel per scale does everything for a frame while
 // it sits in shared memory:
-//   reflect-pad gather + periodic Hann -> ONE complex FFT for the (pred, true) pair of a frame
-//   (z = w*x_pred + i w*x_true, split by Hermitian symmetry) -> power spectra -> both L1 terms
-//   -> d loss / d S_pred -> inverse FFT of 2*X_pred*dS (upper half zero, real part) -> window ->
-//   overlap-add into d loss / d x_pred with the adjoint of the reflect pad.
+//   reflect-pad gather + periodic Hann -> one complex FFT per PAIR of consecutive frames of the same signal
+//   (z = w*frame_a + i w*frame_b, split by Hermitian symmetry; frames of one signal have like magnitudes, so
+//   the packing costs sqrt(2) in rounding error instead of coupling pred to true) -> power spectra -> both L1
+//   terms -> d loss / d S_pred -> ONE inverse FFT for the pair (Hermitian-extended gradient spectra as real /
+//   imaginary part) -> window -> overlap-add into d loss / d x_pred with the adjoint of the reflect pad.
 // The spectrograms never reach HBM; the gradient is produced in the forward pass (the loss is a scalar, so
 // backward is one multiply by the upstream scalar).
 #include "ddsp_common.cuh"
@@ -25,8 +26,8 @@ __device__ __forceinline__ int reflect_index(int p, int N) {
 }
 
 struct MssGeom {
-    int gs;       // threads per frame
-    int fc;       // frames processed concurrently by a CTA
+    int gs;       // threads per frame PAIR (one complex transform carries two frames of the same signal)
+    int fc;       // frame pairs processed concurrently by a CTA
 };
 
 __host__ __device__ inline MssGeom mss_geom(int n) {
@@ -36,9 +37,17 @@ __host__ __device__ inline MssGeom mss_geom(int n) {
     return g;
 }
 
+__host__ __device__ inline size_t mss_group_floats(int n) { return 4 * (size_t)n + (size_t)n + 4; }   // A, B (float2[n] each) + S_true of both frames
+
 __host__ __device__ inline size_t mss_smem_bytes(int n) {
     const MssGeom g = mss_geom(n);
-    return sizeof(float2) * n /*tw*/ + sizeof(float) * n /*window*/ + sizeof(float2) * 2 * (size_t)n * g.fc;
+    return sizeof(float2) * n /*tw*/ + sizeof(float) * n /*window*/ + sizeof(float) * mss_group_floats(n) * g.fc;
+}
+
+// split of a packed transform Z = FFT(xa + i xb):  Xa_k = (Z_k + conj Z_{n-k})/2,  Xb_k = (Z_k - conj Z_{n-k})/(2i)
+__device__ __forceinline__ void split_pair(float2 zk, float2 zn, float2& xa, float2& xb) {
+    xa = make_float2(0.5f * (zk.x + zn.x), 0.5f * (zk.y - zn.y));
+    xb = make_float2(0.5f * (zk.y + zn.y), -0.5f * (zk.x - zn.x));
 }
 
 __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __restrict__ xp, const float* __restrict__ xt,
@@ -48,67 +57,96 @@ __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __r
     extern __shared__ __align__(16) unsigned char mss_raw[];
     float2* tw = reinterpret_cast<float2*>(mss_raw);
     float* win = reinterpret_cast<float*>(tw + n);
-    float2* bufs = reinterpret_cast<float2*>(win + n);
+    float* groups = win + n;
     __shared__ double red[2][MSS_THREADS / 32];
 
     const MssGeom geo = mss_geom(n);
     const int tid = threadIdx.x;
     const int grp = tid / geo.gs, gtid = tid % geo.gs;
     const int b = blockIdx.y;
-    float2* A = bufs + (size_t)grp * 2 * n;
+    float2* A = reinterpret_cast<float2*>(groups + (size_t)grp * mss_group_floats(n));
     float2* Bf = A + n;
+    float* St = reinterpret_cast<float*>(Bf + n);      // [2][half+1] power spectra of the two true frames
     const float* xpb = xp + (size_t)b * N;
     const float* xtb = xt + (size_t)b * N;
     float* gxb = gx ? gx + (size_t)b * N : nullptr;
+    const int half = n / 2;
 
     fft_fill_twiddles(tw, n);
-    for (int m = tid; m < n; m += MSS_THREADS) win[m] = 0.5f - 0.5f * cospif(2.0f * (float)m / (float)n);   // periodic Hann
+    __syncthreads();
+    for (int m = tid; m < n; m += MSS_THREADS) win[m] = 0.5f - 0.5f * tw[m].x;     // periodic Hann, cos from the fp64-rounded table
     __syncthreads();
 
     const float w_lin = (float)inv_count, w_log = (float)(alpha_d * inv_count);
     const float inv_ln2 = 1.4426950408889634f;
     double acc_lin = 0.0, acc_log = 0.0;
-    const int half = n / 2;
     for (int it = 0; it < MSS_ITERS; ++it) {
-        const int f = (blockIdx.x * MSS_ITERS + it) * geo.fc + grp;
-        const bool live = f < F;                       // dead groups still walk through every barrier
-        const int p0 = f * hop - half;
+        const int fa = 2 * ((blockIdx.x * MSS_ITERS + it) * geo.fc + grp), fb = fa + 1;
+        const bool live_a = fa < F, live_b = fb < F;   // dead groups still walk through every barrier
+        const int pa = fa * hop - half, pb = fb * hop - half;
+
+        // ---- true frames: power spectra only -----------------------------------------------------
         for (int m = gtid; m < n; m += geo.gs) {
-            float2 v = make_float2(0.f, 0.f);
-            if (live) {
-                const int idx = reflect_index(p0 + m, N);
-                const float w = win[m];
-                v = make_float2(w * xpb[idx], w * xtb[idx]);
+            const float w = win[m];
+            A[m] = make_float2(live_a ? w * xtb[reflect_index(pa + m, N)] : 0.f, live_b ? w * xtb[reflect_index(pb + m, N)] : 0.f);
+        }
+        __syncthreads();
+        {
+            const float2* Z = block_fft<false>(A, Bf, tw, n, gtid, geo.gs);
+            for (int k = gtid; k <= half; k += geo.gs) {
+                float2 xa, xb;
+                split_pair(Z[k], Z[(n - k) & (n - 1)], xa, xb);
+                St[k] = xa.x * xa.x + xa.y * xa.y;
+                St[half + 1 + k] = xb.x * xb.x + xb.y * xb.y;
             }
-            A[m] = v;
+        }
+        __syncthreads();
+        // ---- predicted frames: loss terms and gradient spectra -----------------------------------
+        for (int m = gtid; m < n; m += geo.gs) {
+            const float w = win[m];
+            A[m] = make_float2(live_a ? w * xpb[reflect_index(pa + m, N)] : 0.f, live_b ? w * xpb[reflect_index(pb + m, N)] : 0.f);
         }
         __syncthreads();
         float2* Z = block_fft<false>(A, Bf, tw, n, gtid, geo.gs);
         float2* Y = (Z == A) ? Bf : A;
-        for (int k = gtid; k < n; k += geo.gs) {
-            float2 yk = make_float2(0.f, 0.f);
-            if (k <= half && live) {
-                const float2 zk = Z[k], zn = Z[(n - k) & (n - 1)];
-                // X_pred = (Z_k + conj Z_{n-k})/2 ;  X_true = (Z_k - conj Z_{n-k})/(2i)
-                const float pr = 0.5f * (zk.x + zn.x), pi = 0.5f * (zk.y - zn.y);
-                const float tr = 0.5f * (zk.y + zn.y), ti = -0.5f * (zk.x - zn.x);
-                const float sp = pr * pr + pi * pi, st = tr * tr + ti * ti;        // power=2 spectrogram
-                const float dl = sp - st;
-                const float lp = log2f(sp + eps), lt = log2f(st + eps);
-                const float dq = lp - lt;
-                acc_lin += (double)fabsf(dl);
-                acc_log += (double)fabsf(dq);
-                const float sl = (dl > 0.f) - (dl < 0.f), sq = (dq > 0.f) - (dq < 0.f);
-                const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);  // d loss / d S_pred
-                yk = make_float2(2.f * pr * gs_, 2.f * pi * gs_);
+        for (int k = gtid; k <= half; k += geo.gs) {
+            float2 xv[2];
+            split_pair(Z[k], Z[(n - k) & (n - 1)], xv[0], xv[1]);
+            float2 G[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                G[e] = make_float2(0.f, 0.f);
+                if (e == 0 ? live_a : live_b) {
+                    const float sp = xv[e].x * xv[e].x + xv[e].y * xv[e].y, st = St[e * (half + 1) + k];   // power=2 spectrogram
+                    const float dl = sp - st;
+                    const float dq = log2f(sp + eps) - log2f(st + eps);
+                    acc_lin += (double)fabsf(dl);
+                    acc_log += (double)fabsf(dq);
+                    const float sl = (dl > 0.f) - (dl < 0.f), sq = (dq > 0.f) - (dq < 0.f);
+                    const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);                     // d loss / d S_pred
+                    G[e] = make_float2(2.f * xv[e].x * gs_, 2.f * xv[e].y * gs_);                          // d loss / d X_pred
+                }
             }
-            if (gxb) Y[k] = yk;
+            if (gxb) {
+                // x-gradient of a frame = w * Re sum_{k<=n/2} G_k e^{+i 2 pi jk/n}: Hermitian-extend G (halved off the
+                // edges) so the inverse transform is real, and carry the two frames as real / imaginary part
+                if (k == 0 || k == half) {
+                    Y[k] = make_float2(G[0].x, G[1].x);
+                } else {
+                    Y[k] = make_float2(0.5f * (G[0].x - G[1].y), 0.5f * (G[0].y + G[1].x));
+                    Y[n - k] = make_float2(0.5f * (G[0].x + G[1].y), 0.5f * (G[1].x - G[0].y));
+                }
+            }
         }
         __syncthreads();
         if (gxb) {
             const float2* R = block_fft<true>(Y, Z, tw, n, gtid, geo.gs);
-            if (live)
-                for (int m = gtid; m < n; m += geo.gs) atomicAdd(&gxb[reflect_index(p0 + m, N)], R[m].x * win[m]);
+            for (int m = gtid; m < n; m += geo.gs) {
+                const float2 r = R[m];
+                const float w = win[m];
+                if (live_a) atomicAdd(&gxb[reflect_index(pa + m, N)], r.x * w);
+                if (live_b) atomicAdd(&gxb[reflect_index(pb + m, N)], r.y * w);
+            }
             __syncthreads();
         }
     }
@@ -155,7 +193,9 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
         DDSP_REQUIRE(n / 2 < N, "ddsp_mss_forward: reflect padding n_fft/2=%d needs a signal longer than that (N=%d)", n / 2, N);
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    cudaError_t e = cudaMemsetAsync(loss_terms, 0, sizeof(double) * (1 + 2 * (size_t)n_scales), st);
+    cudaError_t e = fft_ensure_table(st);
+    DDSP_REQUIRE(e == cudaSuccess, "ddsp_mss_forward: twiddle table initialisation failed: %s", cudaGetErrorString(e));
+    e = cudaMemsetAsync(loss_terms, 0, sizeof(double) * (1 + 2 * (size_t)n_scales), st);
     if (e == cudaSuccess && gx) e = cudaMemsetAsync(gx, 0, sizeof(float) * (size_t)B * N, st);
     DDSP_REQUIRE(e == cudaSuccess, "ddsp_mss_forward: memset failed: %s", cudaGetErrorString(e));
     for (int s = 0; s < n_scales; ++s) {
@@ -168,7 +208,7 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
             DDSP_REQUIRE(e == cudaSuccess, "mss_scale_kernel: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
         }
         const double count = (double)ddsp_mss_count(B, N, n, hop);
-        const int per_cta = g.fc * MSS_ITERS;
+        const int per_cta = 2 * g.fc * MSS_ITERS;
         mss_scale_kernel<<<dim3((F + per_cta - 1) / per_cta, B), MSS_THREADS, smem, st>>>(
             x_pred, x_true, loss_terms, loss_terms + 1 + 2 * s, gx, N, n, hop, F, 1.0 / count, (double)alpha, eps);
         DDSP_CHECK_LAUNCH("mss_scale_kernel");

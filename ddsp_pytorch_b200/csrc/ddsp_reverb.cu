@@ -267,6 +267,13 @@ static int conv_smem_attr() {
     return 0;
 }
 
+static int conv_setup(cudaStream_t st) {
+    if (conv_smem_attr()) return 1;
+    cudaError_t e = fft_ensure_table(st);
+    DDSP_REQUIRE(e == cudaSuccess, "conv: twiddle table initialisation failed: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 static int check_conv(const char* fn, int B, int N, int Lk) {
     DDSP_REQUIRE(B >= 1 && B <= 2 * 65535, "%s: B=%d out of range", fn, B);
     DDSP_REQUIRE(N >= 1 && Lk >= 1, "%s: N=%d, Lk=%d must be positive", fn, N, Lk);
@@ -303,8 +310,8 @@ extern "C" size_t ddsp_conv_scratch_bytes(int B, int N, int Lk) {
 extern "C" int ddsp_conv_forward(const float* x, const float* ir, float* y, void* scratch, int B, int N, int Lk, void* stream) {
     if (check_conv("ddsp_conv_forward", B, N, Lk)) return 1;
     DDSP_REQUIRE(x && ir && y && scratch, "ddsp_conv_forward: null pointer argument");
-    if (conv_smem_attr()) return 1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (conv_setup(st)) return 1;
     const ConvPlan p = conv_plan(B, N, Lk);
     char* base = reinterpret_cast<char*>(scratch);
     float2* Hf = reinterpret_cast<float2*>(base + p.off_H);
@@ -324,8 +331,8 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
                                   int N, int Lk, void* stream) {
     if (check_conv("ddsp_conv_backward", B, N, Lk)) return 1;
     DDSP_REQUIRE(g && ir && scratch && (gx || gir) && (x || !gir), "ddsp_conv_backward: null pointer argument");
-    if (conv_smem_attr()) return 1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (conv_setup(st)) return 1;
     const ConvPlan p = conv_plan(B, N, Lk);
     char* base = reinterpret_cast<char*>(scratch);
     float2* Hf = reinterpret_cast<float2*>(base + p.off_H);

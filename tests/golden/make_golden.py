@@ -207,4 +207,4 @@ if __name__ == "__main__":
     reverb_case("ref_reverb_crop.npz", B=2, N=512, sr=1000, seed=10)           # N < L: IR cropped (reverb.py:34)
     reverb_live_case("ref_reverb_live.npz", sr=1000, block=256, calls=3, seed=11)
     mss_case("ref_mss.npz", B=2, N=4096, n_ffts=[2048, 1024, 512, 256, 128, 64], seed=12)
-    path_case("ref_path.npz", B=2, T=12, K=20, NB=17, sr=1000, hop=64, seed=13)
+    path_case("ref_path.npz", B=2, T=12, K=20, NB=17, sr=4000, hop=64, seed=13)
