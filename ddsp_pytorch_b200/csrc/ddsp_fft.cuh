@@ -28,6 +28,7 @@ __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(
 // Each translation unit owns a copy, filled once per device by the first call that needs it.
 constexpr int FFT_MAX = 4096;
 static __device__ float2 g_fft_tw[FFT_MAX];
+static __device__ double2 g_fft_tw64[FFT_MAX];          // same table in fp64, read straight from global/L1 by block_fft64
 
 static __global__ void fft_init_table_kernel() {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -35,6 +36,7 @@ static __global__ void fft_init_table_kernel() {
         double sn, cs;
         sincospi(2.0 * (double)q / (double)FFT_MAX, &sn, &cs);
         g_fft_tw[q] = make_float2((float)cs, (float)-sn);
+        g_fft_tw64[q] = make_double2(cs, -sn);
     }
 }
 
@@ -96,6 +98,51 @@ __device__ __forceinline__ float2* block_fft(float2* a, float2* b, const float2*
         }
         __syncthreads();
         float2* s = a; a = b; b = s;
+    }
+    return a;
+}
+
+// fp64 variant (same index algebra) for transforms whose small bins feed an ill-conditioned gradient (the
+// log-spectral term of the loss).  Twiddles come from the global fp64 table, stride FFT_MAX/n.
+__device__ __forceinline__ double2 cmul64(double2 a, double2 b) {
+    return make_double2(fma(a.x, b.x, -a.y * b.y), fma(a.x, b.y, a.y * b.x));
+}
+
+__device__ __forceinline__ double2* block_fft64(double2* a, double2* b, int n, int gtid, int gsize) {
+    int p = 1;
+    const int log2n = 31 - __clz(n);
+    const int tscale = FFT_MAX / n;
+    if (log2n & 1) {
+        const int t = n >> 1;
+        for (int i = gtid; i < t; i += gsize) {
+            const double2 u0 = a[i], u1 = a[i + t];
+            b[2 * i] = make_double2(u0.x + u1.x, u0.y + u1.y);
+            b[2 * i + 1] = make_double2(u0.x - u1.x, u0.y - u1.y);
+        }
+        __syncthreads();
+        double2* s = a; a = b; b = s;
+        p = 2;
+    }
+    const int t = n >> 2;
+    for (; p < n; p <<= 2) {
+        const int tstep = n / (4 * p) * tscale;
+        for (int i = gtid; i < t; i += gsize) {
+            const int k = i & (p - 1);
+            const int j = ((i - k) << 2) + k;
+            const double2 u0 = a[i];
+            const double2 u1 = cmul64(a[i + t], g_fft_tw64[k * tstep]);
+            const double2 u2 = cmul64(a[i + 2 * t], g_fft_tw64[2 * k * tstep]);
+            const double2 u3 = cmul64(a[i + 3 * t], g_fft_tw64[3 * k * tstep]);
+            const double2 v0 = make_double2(u0.x + u2.x, u0.y + u2.y), v1 = make_double2(u0.x - u2.x, u0.y - u2.y);
+            const double2 v2 = make_double2(u1.x + u3.x, u1.y + u3.y);
+            const double2 v3 = make_double2(u1.y - u3.y, -(u1.x - u3.x));      // -i * (u1-u3)
+            b[j] = make_double2(v0.x + v2.x, v0.y + v2.y);
+            b[j + p] = make_double2(v1.x + v3.x, v1.y + v3.y);
+            b[j + 2 * p] = make_double2(v0.x - v2.x, v0.y - v2.y);
+            b[j + 3 * p] = make_double2(v1.x - v3.x, v1.y - v3.y);
+        }
+        __syncthreads();
+        double2* s = a; a = b; b = s;
     }
     return a;
 }

@@ -37,7 +37,8 @@ __host__ __device__ inline MssGeom mss_geom(int n) {
     return g;
 }
 
-__host__ __device__ inline size_t mss_group_floats(int n) { return 4 * (size_t)n + (size_t)n + 4; }   // A, B (float2[n] each) + S_true of both frames
+// per group: two double2[n] buffers (the fp32 transforms alias them) + S_true of both frames
+__host__ __device__ inline size_t mss_group_floats(int n) { return 8 * (size_t)n + (size_t)n + 4; }
 
 __host__ __device__ inline size_t mss_smem_bytes(int n) {
     const MssGeom g = mss_geom(n);
@@ -52,8 +53,9 @@ __device__ __forceinline__ void split_pair(float2 zk, float2 zn, float2& xa, flo
 
 __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __restrict__ xp, const float* __restrict__ xt,
                                                                 double* __restrict__ loss, double* __restrict__ terms,
-                                                                float* __restrict__ gx, int N, int n, int hop, int F,
-                                                                double inv_count, double alpha_d, float eps) {
+                                                                float* __restrict__ gx, const float* __restrict__ window,
+                                                                int N, int n, int hop, int F, double inv_count, double alpha_d,
+                                                                float eps) {
     extern __shared__ __align__(16) unsigned char mss_raw[];
     float2* tw = reinterpret_cast<float2*>(mss_raw);
     float* win = reinterpret_cast<float*>(tw + n);
@@ -64,9 +66,11 @@ __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __r
     const int tid = threadIdx.x;
     const int grp = tid / geo.gs, gtid = tid % geo.gs;
     const int b = blockIdx.y;
-    float2* A = reinterpret_cast<float2*>(groups + (size_t)grp * mss_group_floats(n));
+    double2* Ad = reinterpret_cast<double2*>(groups + (size_t)grp * mss_group_floats(n));
+    double2* Bd = Ad + n;
+    float2* A = reinterpret_cast<float2*>(Ad);         // fp32 ping-pong pair inside the first fp64 buffer
     float2* Bf = A + n;
-    float* St = reinterpret_cast<float*>(Bf + n);      // [2][half+1] power spectra of the two true frames
+    float* St = reinterpret_cast<float*>(Bd + n);      // [2][half+1] power spectra of the two true frames
     const float* xpb = xp + (size_t)b * N;
     const float* xtb = xt + (size_t)b * N;
     float* gxb = gx ? gx + (size_t)b * N : nullptr;
@@ -74,7 +78,9 @@ __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __r
 
     fft_fill_twiddles(tw, n);
     __syncthreads();
-    for (int m = tid; m < n; m += MSS_THREADS) win[m] = 0.5f - 0.5f * tw[m].x;     // periodic Hann, cos from the fp64-rounded table
+    // the reference's window is the fp32 buffer of its Spectrogram module (mss_loss.py:23); use the caller's copy of
+    // it when given so both sides window with the same values, else the periodic Hann from the fp64-rounded table
+    for (int m = tid; m < n; m += MSS_THREADS) win[m] = window ? window[m] : 0.5f - 0.5f * tw[m].x;
     __syncthreads();
 
     const float w_lin = (float)inv_count, w_log = (float)(alpha_d * inv_count);
@@ -101,30 +107,33 @@ __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __r
             }
         }
         __syncthreads();
-        // ---- predicted frames: loss terms and gradient spectra -----------------------------------
+        // ---- predicted frames in fp64: their small bins decide d log2(S+eps)/dx -----------------------
         for (int m = gtid; m < n; m += geo.gs) {
-            const float w = win[m];
-            A[m] = make_float2(live_a ? w * xpb[reflect_index(pa + m, N)] : 0.f, live_b ? w * xpb[reflect_index(pb + m, N)] : 0.f);
+            const double w = (double)win[m];
+            Ad[m] = make_double2(live_a ? w * (double)xpb[reflect_index(pa + m, N)] : 0.0,
+                                 live_b ? w * (double)xpb[reflect_index(pb + m, N)] : 0.0);
         }
         __syncthreads();
-        float2* Z = block_fft<false>(A, Bf, tw, n, gtid, geo.gs);
-        float2* Y = (Z == A) ? Bf : A;
+        const double2* Z = block_fft64(Ad, Bd, n, gtid, geo.gs);
+        float2* Y = reinterpret_cast<float2*>(Z == Ad ? Bd : Ad);      // the free fp64 buffer holds the fp32 inverse pair
+        float2* Y2 = Y + n;
         for (int k = gtid; k <= half; k += geo.gs) {
-            float2 xv[2];
-            split_pair(Z[k], Z[(n - k) & (n - 1)], xv[0], xv[1]);
+            const double2 zk = Z[k], zn = Z[(n - k) & (n - 1)];
+            const double xr[2] = {0.5 * (zk.x + zn.x), 0.5 * (zk.y + zn.y)};
+            const double xi[2] = {0.5 * (zk.y - zn.y), -0.5 * (zk.x - zn.x)};
             float2 G[2];
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 G[e] = make_float2(0.f, 0.f);
                 if (e == 0 ? live_a : live_b) {
-                    const float sp = xv[e].x * xv[e].x + xv[e].y * xv[e].y, st = St[e * (half + 1) + k];   // power=2 spectrogram
+                    const float sp = (float)(xr[e] * xr[e] + xi[e] * xi[e]), st = St[e * (half + 1) + k];   // power=2 spectrogram
                     const float dl = sp - st;
                     const float dq = log2f(sp + eps) - log2f(st + eps);
                     acc_lin += (double)fabsf(dl);
                     acc_log += (double)fabsf(dq);
                     const float sl = (dl > 0.f) - (dl < 0.f), sq = (dq > 0.f) - (dq < 0.f);
-                    const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);                     // d loss / d S_pred
-                    G[e] = make_float2(2.f * xv[e].x * gs_, 2.f * xv[e].y * gs_);                          // d loss / d X_pred
+                    const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);                      // d loss / d S_pred
+                    G[e] = make_float2(2.f * (float)xr[e] * gs_, 2.f * (float)xi[e] * gs_);                 // d loss / d X_pred
                 }
             }
             if (gxb) {
@@ -140,7 +149,7 @@ __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __r
         }
         __syncthreads();
         if (gxb) {
-            const float2* R = block_fft<true>(Y, Z, tw, n, gtid, geo.gs);
+            const float2* R = block_fft<true>(Y, Y2, tw, n, gtid, geo.gs);
             for (int m = gtid; m < n; m += geo.gs) {
                 const float2 r = R[m];
                 const float w = win[m];
@@ -182,8 +191,8 @@ extern "C" int64_t ddsp_mss_count(int B, int N, int n_fft, int hop) {
 }
 
 extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double* loss_terms, float* loss_f32, float* gx,
-                                const int* n_ffts_host, const int* hops_host, int n_scales, float alpha, float eps, int B, int N,
-                                void* stream) {
+                                const int* n_ffts_host, const int* hops_host, const float* const* windows_host, int n_scales,
+                                float alpha, float eps, int B, int N, void* stream) {
     DDSP_REQUIRE(x_pred && x_true && loss_terms && n_ffts_host && hops_host, "ddsp_mss_forward: null pointer argument");
     DDSP_REQUIRE(B >= 1 && B <= 65535 && N >= 2 && n_scales >= 1 && n_scales <= 64, "ddsp_mss_forward: bad B/N/n_scales");
     for (int s = 0; s < n_scales; ++s) {
@@ -210,7 +219,8 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
         const double count = (double)ddsp_mss_count(B, N, n, hop);
         const int per_cta = 2 * g.fc * MSS_ITERS;
         mss_scale_kernel<<<dim3((F + per_cta - 1) / per_cta, B), MSS_THREADS, smem, st>>>(
-            x_pred, x_true, loss_terms, loss_terms + 1 + 2 * s, gx, N, n, hop, F, 1.0 / count, (double)alpha, eps);
+            x_pred, x_true, loss_terms, loss_terms + 1 + 2 * s, gx, windows_host ? windows_host[s] : nullptr, N, n, hop, F,
+            1.0 / count, (double)alpha, eps);
         DDSP_CHECK_LAUNCH("mss_scale_kernel");
     }
     if (loss_f32) {

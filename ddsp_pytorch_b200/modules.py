@@ -117,7 +117,7 @@ class SSSLoss(nn.Module):
         self.stft = _HannWindowHolder(n_fft)
 
     def forward(self, x_pred, x_true):
-        return ops.mss_loss(x_pred, x_true, [self.n_fft], self.alpha, self.overlap, self.eps)
+        return ops.mss_loss(x_pred, x_true, [self.n_fft], self.alpha, self.overlap, self.eps, windows=[self.stft.window])
 
 
 class MSSLoss(nn.Module):
@@ -134,4 +134,5 @@ class MSSLoss(nn.Module):
             x_pred = x_pred[self.signal_key]
         if isinstance(x_true, dict):
             x_true = x_true["audio"]
-        return ops.mss_loss(x_pred, x_true, self.n_ffts, self.alpha, self.overlap, self.eps)
+        return ops.mss_loss(x_pred, x_true, self.n_ffts, self.alpha, self.overlap, self.eps,
+                            windows=[m.stft.window for m in self.losses])

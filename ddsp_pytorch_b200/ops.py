@@ -250,7 +250,7 @@ def reverb_live(buffer: torch.Tensor, x: torch.Tensor, ir: torch.Tensor) -> torc
 # ------------------------------------------------------------------------------------------------------
 class _MSSLoss(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x_pred, x_true, n_ffts, hops, alpha: float, eps: float):
+    def forward(ctx, x_pred, x_true, n_ffts, hops, alpha: float, eps: float, windows):
         import ctypes as C
         xp, xt = _f32(x_pred), _f32(x_true)
         if xp.dim() != 2 or xp.shape != xt.shape:
@@ -264,10 +264,17 @@ class _MSSLoss(torch.autograd.Function):
         gx = torch.empty(B, N, dtype=torch.float32, device=dev) if need_grad else None
         nf = (C.c_int * ns)(*[int(v) for v in n_ffts])
         hp = (C.c_int * ns)(*[int(v) for v in hops])
+        wins = None
+        if windows is not None:
+            keep = [None if w is None else w.detach().to(device=dev, dtype=torch.float32).contiguous() for w in windows]
+            for w, n in zip(keep, n_ffts):
+                if w is not None and w.numel() != n:
+                    raise RuntimeError(f"mss_loss: window of {w.numel()} samples given for n_fft={n}")
+            wins = (C.c_void_p * ns)(*[None if w is None else w.data_ptr() for w in keep])
         with torch.cuda.device(dev):
             _lib.call("ddsp_mss_forward", xp.data_ptr(), xt.data_ptr(), terms.data_ptr(), loss.data_ptr(),
-                      gx.data_ptr() if need_grad else None, C.cast(nf, C.c_void_p), C.cast(hp, C.c_void_p), ns, float(alpha),
-                      float(eps), B, N, _stream())
+                      gx.data_ptr() if need_grad else None, C.cast(nf, C.c_void_p), C.cast(hp, C.c_void_p),
+                      C.cast(wins, C.c_void_p) if wins is not None else None, ns, float(alpha), float(eps), B, N, _stream())
         if need_grad:
             ctx.save_for_backward(gx)
         ctx.meta = (x_pred.dtype, B, N)
@@ -282,13 +289,15 @@ class _MSSLoss(torch.autograd.Function):
         out = torch.empty_like(gx)
         with torch.cuda.device(gx.device):
             _lib.call("ddsp_mss_backward", gl.data_ptr(), gx.data_ptr(), out.data_ptr(), B, N, _stream())
-        return out.to(dt), None, None, None, None, None
+        return out.to(dt), None, None, None, None, None, None
 
 
-def mss_loss(x_pred, x_true, n_ffts, alpha: float = 1.0, overlap: float = 0.75, eps: float = 1e-7) -> torch.Tensor:
-    """MSSLoss.forward (mss_loss.py:57-68) on tensors [B,N] -> 0-dim fp32 loss; gradient flows to x_pred only."""
+def mss_loss(x_pred, x_true, n_ffts, alpha: float = 1.0, overlap: float = 0.75, eps: float = 1e-7, windows=None) -> torch.Tensor:
+    """MSSLoss.forward (mss_loss.py:57-68) on tensors [B,N] -> 0-dim fp32 loss; gradient flows to x_pred only.
+    ``windows``: optional per-scale fp32 analysis windows (the modules pass their ``stft.window`` buffers)."""
     hops = [int(n * (1 - overlap)) for n in n_ffts]          # mss_loss.py:21
-    return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps))
+    return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps),
+                          None if windows is None else tuple(windows))
 
 
 def oscillator_live(f0, c, a, last_phases, sample_rate: int, hop: int):

@@ -145,10 +145,13 @@ int64_t ddsp_mss_count(int B, int N, int n_fft, int hop);
  *     sum_s ( sum|Sp-St| + alpha*sum|log2(St+eps)-log2(Sp+eps)| ) / count_s, then per scale the two raw sums;
  *   loss_f32 (device float[1]) or NULL: the loss rounded to fp32;
  *   gx [B,N] or NULL (zeroed here): d loss / d x_pred, produced in the same pass.
- *   n_ffts_host / hops_host: HOST int arrays; n_fft a power of two in [4,4096], n_fft/2 < N. */
+ *   n_ffts_host / hops_host: HOST int arrays; n_fft a power of two in [4,4096], n_fft/2 < N;
+ *   windows_host: NULL, or a HOST array of n_scales device pointers (entries may be NULL) to the fp32 analysis
+ *     windows [n_fft] -- the reference's `stft.window` buffers (mss_loss.py:23); NULL = periodic Hann. */
 int ddsp_mss_forward(const float* x_pred, const float* x_true, double* loss_terms, float* loss_f32,
-                     float* gx, const int* n_ffts_host, const int* hops_host, int n_scales, float alpha,
-                     float eps, int B, int N, void* stream);
+                     float* gx, const int* n_ffts_host, const int* hops_host,
+                     const float* const* windows_host, int n_scales, float alpha, float eps, int B, int N,
+                     void* stream);
 
 /* Backward of the scalar loss: gx_out = gloss[0] * gx_saved   (gloss: device float scalar). */
 int ddsp_mss_backward(const float* gloss, const float* gx_saved, float* gx_out, int B, int N,

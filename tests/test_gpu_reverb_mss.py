@@ -84,7 +84,7 @@ def test_mss_golden(golden):
     assert abs(float(loss) - float(g["loss64"])) <= TOL * float(g["loss64"])
     loss.backward()
     # norm-wise; the fp32 reference itself sits at 5e-5..2.5e-4 here (d log2(S+eps) is ill-conditioned)
-    assert l2rel(xp.grad, g["gx"]) <= 2e-4
+    assert l2rel(xp.grad, g["gx"]) <= TOL
     for n, want in zip(n_ffts, g["per_scale64"]):
         assert abs(float(ops.mss_loss(xp.detach(), xt, [n])) - float(want)) <= TOL * float(want)
 
@@ -104,19 +104,19 @@ def test_mss_against_oracle(B, N, n_ffts):
     (O.mss_loss(xp32, xt, n_ffts) * 0.7).backward()          # the reference's own fp32 arithmetic, for scale
     ref32_err = l2rel(xp32.grad, xpd.grad)
     xpc = xp.cuda().requires_grad_(True)
-    got = ops.mss_loss(xpc, xt.cuda(), n_ffts)
+    got = ops.mss_loss(xpc, xt.cuda(), n_ffts, windows=[torch.hann_window(n) for n in n_ffts])
     (got * 0.7).backward()
     err = l2rel(xpc.grad, xpd.grad)
     print(f"MSS grad {n_ffts}: |cuda-ref64|/|ref64| = {err:.2e}, reference fp32 vs fp64 = {ref32_err:.2e}")
     assert abs(float(got) - float(want)) <= TOL * float(want)
-    assert err <= max(TOL, 1.5 * ref32_err)
+    assert err <= TOL
 
 
 def test_mss_dict_inputs_and_identity():
     import ddsp_pytorch_b200 as d
     x = torch.randn(2, 4096).cuda() * 0.1
     m = d.MSSLoss([256, 64])
-    assert float(m({"audio_reverb": x, "hidden": None}, {"audio": x})) == 0.0     # same frames, same arithmetic
+    assert float(m({"audio_reverb": x, "hidden": None}, {"audio": x})) < 1e-6     # pred goes through fp64, true through fp32
 
 
 def test_osc_live_golden(golden):
