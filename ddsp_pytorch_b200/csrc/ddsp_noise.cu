@@ -290,6 +290,354 @@ __global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict_
     }
 }
 
+// ================================================================================================
+// Fast path (hop % 16 == 0): a TEAM of hop/16 threads owns one frame (one warp at hop = 512), four warps
+// of teams per CTA.  Differences from the generic kernels above:
+//   * noise window in shared memory is padded by 4 floats every 32 (swz) so the stride-16 float4 window
+//     loads of a team are bank-conflict free;
+//   * 16 outputs x 8 taps register tile: 128 FFMA per 4 LDS.128, three rotating 8-float window chunks
+//     (no register shuffling);
+//   * r = irfft(H) by a cosine recurrence over m per output j (no table look-ups), and only for
+//     j <= M/4: cos(2 pi m (M/2-j)/M) = (-1)^m cos(2 pi m j/M), so even/odd partial sums give r[j] and r[M/2-j];
+//   * the wrapped taps' triangular corner is spread over the whole team (one output per thread per pass)
+//     instead of serialising on the threads that own the frame's tail.
+// ================================================================================================
+constexpr int TEAM_BLOCK = 128;
+
+__device__ __forceinline__ int swz(int i) { return i + ((i >> 5) << 2); }
+
+struct TeamLayout {
+    int half, TP, PADL, uc_off, n_H, n_rr, n_u, n_uc, n_cor, total;
+};
+
+__host__ __device__ inline TeamLayout team_layout(int NB, int hop) {
+    TeamLayout L;
+    L.half = NB - 1;
+    L.TP = noise_tp(NB);
+    L.PADL = (L.TP + 16 + 31) & ~31;
+    L.n_H = (NB + 3) & ~3;
+    L.n_rr = (L.half + 1 + 3) & ~3;
+    const int logical = L.PADL + hop;
+    L.n_u = (logical + ((logical >> 5) << 2) + 4 + 3) & ~3;
+    L.n_uc = (2 * L.half + 4 + 3) & ~3;                 // unswizzled copy of u[-half .. half) for the corner
+    L.n_cor = (L.half + 3) & ~3;
+    L.total = L.n_H + L.n_rr + 2 * L.TP + L.n_u + L.n_uc + L.n_cor;
+    const int out_need = hop;                           // the output staging area reuses the u region
+    if (L.n_u < out_need) L.total += out_need - L.n_u;
+    return L;
+}
+
+// r[0..half] from H (team-cooperative); H, rr in shared memory.
+__device__ __forceinline__ void team_build_r(const float* H, float* rr, int NB, int l, int TS) {
+    const int half = NB - 1, M = 2 * half;
+    const float invM = 1.0f / (float)M;
+    for (int j = l; 2 * j <= half; j += TS) {
+        const float sh = sinpif((float)j * invM);       // sin(theta/2), theta = 2 pi j / M <= pi/2
+        const float dl = -4.f * sh * sh;                // 2 cos(theta) - 2
+        float e = 0.5f * dl, c = 1.f + e;               // cos(1*theta)
+        float E = 0.f, O = 0.f;
+        int m = 1;
+        for (; m + 1 < half; m += 2) {
+            O = fmaf(H[m], c, O);
+            e = fmaf(dl, c, e); c += e;
+            E = fmaf(H[m + 1], c, E);
+            e = fmaf(dl, c, e); c += e;
+        }
+        if (m < half) O = fmaf(H[m], c, O);
+        const float h0 = H[0], hN = H[half];
+        const float sj = (j & 1) ? -hN : hN, sk = ((half - j) & 1) ? -hN : hN;
+        rr[j] = (h0 + sj + 2.f * (E + O)) * invM;
+        rr[half - j] = (h0 + sk + 2.f * (E - O)) * invM;
+    }
+}
+
+#define NOISE_TILE(NW, M1, M2, Q0)                                                                              \
+    {                                                                                                           \
+        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz(ub - (Q0) - 8));                            \
+        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz(ub - (Q0) - 4));                            \
+        NW[0] = l0_.x; NW[1] = l0_.y; NW[2] = l0_.z; NW[3] = l0_.w;                                             \
+        NW[4] = l1_.x; NW[5] = l1_.y; NW[6] = l1_.z; NW[7] = l1_.w;                                             \
+        const float4 t0_ = *reinterpret_cast<const float4*>(taps + (Q0));                                       \
+        const float4 t1_ = *reinterpret_cast<const float4*>(taps + (Q0) + 4);                                   \
+        const float tp_[8] = {t0_.x, t0_.y, t0_.z, t0_.w, t1_.x, t1_.y, t1_.z, t1_.w};                          \
+        _Pragma("unroll") for (int d = 0; d < 8; ++d) {                                                         \
+            _Pragma("unroll") for (int r = 0; r < 16; ++r) {                                                    \
+                const int ix = 8 + r - d;                                                                       \
+                const float wv = ix < 8 ? NW[ix] : (ix < 16 ? M1[ix - 8] : M2[ix - 16]);                        \
+                acc[r] = fmaf(tp_[d], wv, acc[r]);                                                              \
+            }                                                                                                   \
+        }                                                                                                       \
+    }
+
+__global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float* __restrict__ H, const float* __restrict__ noise,
+                                                                    float* __restrict__ y, int accumulate, uint2 key,
+                                                                    uint32_t offset, uint32_t voice_offset, int T, int NB, int hop,
+                                                                    long long frames) {
+    extern __shared__ __align__(16) float smem[];
+    const int TS = hop >> 4, FPB = TEAM_BLOCK / TS;
+    const int team = threadIdx.x / TS, l = threadIdx.x % TS;
+    const TeamLayout L = team_layout(NB, hop);
+    float* base = smem + (size_t)team * L.total;
+    float* Hs = base;
+    float* rr = Hs + L.n_H;
+    float* hc = rr + L.n_rr;
+    float* ha = hc + L.TP;
+    float* u = ha + L.TP;                               // swizzled: logical index PADL + j
+    float* uc = u + (L.n_u < hop ? hop : L.n_u);        // uc[half + x] = u[x], x in [-half, half)
+    float* cor = uc + L.n_uc;
+    const int half = L.half, TP = L.TP, PADL = L.PADL;
+    const long long frame = (long long)blockIdx.x * FPB + team;
+    const bool live = frame < frames;
+    const uint32_t b = live ? (uint32_t)(frame / T) : 0u, t = live ? (uint32_t)(frame % T) : 0u;
+
+    // ---- stage 1: H, noise (generated or read), zero pads -----------------------------------------
+    if (live)
+        for (int m = l; m < NB; m += TS) Hs[m] = H[frame * NB + m];
+    for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
+    for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
+    __syncthreads();
+    if (live) {
+        const float* nf = noise ? noise + frame * hop : nullptr;
+        for (int q = l; q < (hop >> 2); q += TS) {
+            const float4 v = nf ? *reinterpret_cast<const float4*>(nf + 4 * q)
+                                : philox_noise4((uint32_t)q, t, voice_offset + b, offset, key);
+            *reinterpret_cast<float4*>(u + swz(PADL + 4 * q)) = v;
+            if (4 * q < half) {
+                const float vv[4] = {v.x, v.y, v.z, v.w};
+                for (int e = 0; e < 4; ++e)
+                    if (4 * q + e < half) uc[half + 4 * q + e] = vv[e];
+            }
+        }
+        team_build_r(Hs, rr, NB, l, TS);
+    }
+    __syncthreads();
+    // ---- stage 2: windowed taps (filtered_noise.py:14-20) -----------------------------------------
+    if (live) {
+        const float invM = 0.5f / (float)half;
+        for (int q = l; q < TP; q += TS) {
+            float c = 0.f, a = 0.f;
+            if (q < half) {
+                const float cq = cospif(2.f * (float)q * invM);
+                c = rr[q] * (0.5f + 0.5f * cq);
+                a = rr[half - q] * (0.5f - 0.5f * cq);
+            }
+            hc[q] = c;
+            ha[q] = a;
+        }
+    }
+    __syncthreads();
+    // ---- stage 3: causal taps, 16 outputs per thread ----------------------------------------------
+    float acc[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) acc[r] = 0.f;
+    if (live) {
+        const int ub = PADL + 16 * l;                   // logical index of this thread's first output
+        float wa[8], wb[8], wc[8];
+        {
+            const float4 a0 = *reinterpret_cast<const float4*>(u + swz(ub)), a1 = *reinterpret_cast<const float4*>(u + swz(ub + 4));
+            const float4 a2 = *reinterpret_cast<const float4*>(u + swz(ub + 8)), a3 = *reinterpret_cast<const float4*>(u + swz(ub + 12));
+            wb[0] = a0.x; wb[1] = a0.y; wb[2] = a0.z; wb[3] = a0.w; wb[4] = a1.x; wb[5] = a1.y; wb[6] = a1.z; wb[7] = a1.w;
+            wc[0] = a2.x; wc[1] = a2.y; wc[2] = a2.z; wc[3] = a2.w; wc[4] = a3.x; wc[5] = a3.y; wc[6] = a3.z; wc[7] = a3.w;
+        }
+        const float* taps = hc;
+        for (int q0 = 0; q0 < TP; q0 += 24) {
+            NOISE_TILE(wa, wb, wc, q0);
+            if (q0 + 8 >= TP) break;
+            NOISE_TILE(wc, wa, wb, q0 + 8);
+            if (q0 + 16 >= TP) break;
+            NOISE_TILE(wb, wc, wa, q0 + 16);
+        }
+        // ---- stage 4: wrapped taps, one corner output per thread per pass -------------------------
+        for (int jp = l; jp < half; jp += TS) {
+            float a2 = 0.f;
+            const float* ux = uc + half + jp;
+            for (int i = 0; i < half; ++i) a2 = fmaf(ha[i], ux[-i], a2);
+            cor[jp] = a2;
+        }
+    }
+    __syncthreads();
+    // ---- stage 5: add the corner, stage through shared memory for coalesced float4 stores ---------
+    float* outs = u;                                    // window no longer needed
+    if (live) {
+        const int jw = hop - half;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const int j = 16 * l + r;
+            if (j >= jw) acc[r] += cor[j - jw];
+        }
+    }
+    __syncthreads();
+    if (live) {
+#pragma unroll
+        for (int r = 0; r < 16; r += 4) *reinterpret_cast<float4*>(outs + 16 * l + r) = make_float4(acc[r], acc[r + 1], acc[r + 2], acc[r + 3]);
+    }
+    __syncthreads();
+    if (live) {
+        float* yp = y + frame * hop;
+        for (int q = l; q < (hop >> 2); q += TS) {
+            float4 o = *reinterpret_cast<const float4*>(outs + 4 * q);
+            if (accumulate) {
+                const float4 p = *reinterpret_cast<const float4*>(yp + 4 * q);
+                o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+            }
+            *reinterpret_cast<float4*>(yp + 4 * q) = o;
+        }
+    }
+}
+
+// ---- backward fast path -------------------------------------------------------------------------
+// Work item (tap group tg of 8 taps, sample slice sl) = 8x8 register tiles over the slice; items are laid out
+// so that the 8 threads of a quarter warp share a slice (g loads broadcast, window loads conflict-free).
+struct TeamBwdLayout {
+    int half, TP, PADL, ntg, nsl, n_u, n_uc, n_g2, n_part, n_dha, n_dr, total;
+};
+
+__host__ __device__ inline TeamBwdLayout team_bwd_layout(int NB, int hop) {
+    TeamBwdLayout L;
+    L.half = NB - 1;
+    L.TP = noise_tp(NB);
+    L.PADL = (L.TP + 16 + 31) & ~31;
+    L.ntg = L.TP / 8;
+    const int TS = hop >> 4;
+    int nsl = 1;
+    while (nsl * 2 * L.ntg <= TS && hop % (16 * nsl) == 0) nsl *= 2;
+    L.nsl = nsl;
+    const int logical = L.PADL + hop;
+    L.n_u = (logical + ((logical >> 5) << 2) + 4 + 3) & ~3;
+    L.n_uc = (2 * L.half + 4 + 3) & ~3;
+    L.n_g2 = (L.half + 3) & ~3;
+    L.n_part = L.TP * nsl;
+    L.n_dha = (L.half + 3) & ~3;
+    L.n_dr = (L.half + 1 + 3) & ~3;
+    L.total = hop + L.n_u + L.n_uc + L.n_g2 + L.n_part + L.n_dha + L.n_dr;
+    return L;
+}
+
+#define NOISE_BTILE(LO, UP, JB)                                                                                 \
+    {                                                                                                           \
+        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz(PADL + (JB) - q0));                         \
+        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz(PADL + (JB) - q0 + 4));                     \
+        UP[0] = l0_.x; UP[1] = l0_.y; UP[2] = l0_.z; UP[3] = l0_.w;                                             \
+        UP[4] = l1_.x; UP[5] = l1_.y; UP[6] = l1_.z; UP[7] = l1_.w;                                             \
+        const float4 g0_ = *reinterpret_cast<const float4*>(gs + (JB));                                         \
+        const float4 g1_ = *reinterpret_cast<const float4*>(gs + (JB) + 4);                                     \
+        const float gv_[8] = {g0_.x, g0_.y, g0_.z, g0_.w, g1_.x, g1_.y, g1_.z, g1_.w};                          \
+        _Pragma("unroll") for (int r = 0; r < 8; ++r) {                                                         \
+            _Pragma("unroll") for (int d = 0; d < 8; ++d) {                                                     \
+                const int ix = 8 + r - d;                                                                       \
+                acc[d] = fmaf(gv_[r], ix < 8 ? LO[ix] : UP[ix - 8], acc[d]);                                    \
+            }                                                                                                   \
+        }                                                                                                       \
+    }
+
+__global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float* __restrict__ g, const float* __restrict__ noise,
+                                                                    float* __restrict__ gH, uint2 key, uint32_t offset,
+                                                                    uint32_t voice_offset, int T, int NB, int hop, long long frames) {
+    extern __shared__ __align__(16) float smem[];
+    const int TS = hop >> 4, FPB = TEAM_BLOCK / TS;
+    const int team = threadIdx.x / TS, l = threadIdx.x % TS;
+    const TeamBwdLayout L = team_bwd_layout(NB, hop);
+    float* gs = smem + (size_t)team * L.total;          // [hop] upstream gradient of the frame
+    float* u = gs + hop;                                // swizzled noise, logical index PADL + j
+    float* uc = u + L.n_u;                              // uc[half + x] = u[x], x in [-half, half)
+    float* g2 = uc + L.n_uc;                            // gradient seen by the wrapped taps
+    float* part = g2 + L.n_g2;                          // [TP][nsl]
+    float* dha = part + L.n_part;
+    float* dr = dha + L.n_dha;
+    const int half = L.half, PADL = L.PADL, nsl = L.nsl, ntg = L.ntg;
+    const long long frame = (long long)blockIdx.x * FPB + team;
+    const bool live = frame < frames;
+    const uint32_t b = live ? (uint32_t)(frame / T) : 0u, t = live ? (uint32_t)(frame % T) : 0u;
+    const int jw = hop - half;
+
+    for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
+    for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
+    __syncthreads();
+    if (live) {
+        const float* gf = g + frame * hop;
+        const float* nf = noise ? noise + frame * hop : nullptr;
+        for (int q = l; q < (hop >> 2); q += TS) {
+            *reinterpret_cast<float4*>(gs + 4 * q) = *reinterpret_cast<const float4*>(gf + 4 * q);
+            const float4 v = nf ? *reinterpret_cast<const float4*>(nf + 4 * q)
+                                : philox_noise4((uint32_t)q, t, voice_offset + b, offset, key);
+            *reinterpret_cast<float4*>(u + swz(PADL + 4 * q)) = v;
+            if (4 * q < half) {
+                const float vv[4] = {v.x, v.y, v.z, v.w};
+                for (int e = 0; e < 4; ++e)
+                    if (4 * q + e < half) uc[half + 4 * q + e] = vv[e];
+            }
+        }
+        for (int i = l; i < L.n_g2; i += TS) g2[i] = i < half ? gf[jw + i] : 0.f;
+    }
+    __syncthreads();
+    if (live) {
+        // ---- d hc[q] = sum_j g[j] u[j-q] ----------------------------------------------------------
+        const int SL = hop / nsl;
+        for (int w = l; w < ntg * nsl; w += TS) {
+            const int sl = w / ntg, tg = w % ntg, q0 = 8 * tg;
+            float acc[8];
+#pragma unroll
+            for (int d = 0; d < 8; ++d) acc[d] = 0.f;
+            float wa[8], wb[8];
+            const int jb0 = sl * SL;
+            {
+                const float4 a0 = *reinterpret_cast<const float4*>(u + swz(PADL + jb0 - q0 - 8));
+                const float4 a1 = *reinterpret_cast<const float4*>(u + swz(PADL + jb0 - q0 - 4));
+                wa[0] = a0.x; wa[1] = a0.y; wa[2] = a0.z; wa[3] = a0.w; wa[4] = a1.x; wa[5] = a1.y; wa[6] = a1.z; wa[7] = a1.w;
+            }
+            for (int jb = jb0; jb < jb0 + SL; jb += 16) {
+                NOISE_BTILE(wa, wb, jb);
+                if (jb + 8 >= jb0 + SL) break;
+                NOISE_BTILE(wb, wa, jb + 8);
+            }
+#pragma unroll
+            for (int d = 0; d < 8; ++d) part[(q0 + d) * nsl + sl] = acc[d];
+        }
+        // ---- d ha[i] = sum_{j'} g[hop-M/2+j'] u[j'-i] ---------------------------------------------
+        for (int i = l; i < half; i += TS) {
+            float a2 = 0.f;
+            const float* ux = uc + half - i;
+            for (int jp = 0; jp < half; ++jp) a2 = fmaf(g2[jp], ux[jp], a2);
+            dha[i] = a2;
+        }
+    }
+    __syncthreads();
+    if (live) {
+        // ---- d r[p] = hann[M/2+p] * (d hc[p] + d ha[M/2-p]) ---------------------------------------
+        const float invh = 1.0f / (float)half;
+        for (int p = l; p <= half; p += TS) {
+            float v = 0.f;
+            if (p < half)
+                for (int i = 0; i < nsl; ++i) v += part[p * nsl + i];
+            if (p >= 1) v += dha[half - p];
+            dr[p] = v * (0.5f + 0.5f * cospif((float)p * invh));
+        }
+    }
+    __syncthreads();
+    if (live) {
+        // ---- d H[m] = kappa_m/M sum_p d r[p] cos(2 pi m p/M); m and M/2-m share even/odd partial sums
+        const int M = 2 * half;
+        const float invM = 1.0f / (float)M;
+        for (int m = l; 2 * m <= half; m += TS) {
+            const float sh = sinpif((float)m * invM);
+            const float dl = -4.f * sh * sh;
+            float e = -0.5f * dl, c = 1.f;
+            float E = 0.f, O = 0.f;
+            int p = 0;
+            for (; p + 1 <= half; p += 2) {
+                E = fmaf(dr[p], c, E);
+                e = fmaf(dl, c, e); c += e;
+                O = fmaf(dr[p + 1], c, O);
+                e = fmaf(dl, c, e); c += e;
+            }
+            if (p <= half) E = fmaf(dr[p], c, E);
+            const int m2 = half - m;
+            gH[frame * NB + m] = (E + O) * ((m == 0 || m == half) ? invM : 2.f * invM);
+            gH[frame * NB + m2] = (E - O) * ((m2 == 0 || m2 == half) ? invM : 2.f * invM);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // small utility kernels
 // ------------------------------------------------------------------------------------------------
@@ -355,9 +703,21 @@ extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, 
                                   uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop, void* stream) {
     if (check_noise_shape("ddsp_noise_forward", B, T, NB, hop)) return 1;
     DDSP_REQUIRE(H && y, "ddsp_noise_forward: null pointer argument");
+    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
+    if (hop % 16 == 0 && hop / 16 <= TEAM_BLOCK && TEAM_BLOCK % (hop / 16) == 0) {
+        const int FPB = TEAM_BLOCK / (hop / 16);
+        const size_t tsm = sizeof(float) * (size_t)team_layout(NB, hop).total * FPB;
+        if (tsm <= 200 * 1024) {
+            if (reserve_smem(noise_fwd_team_kernel, tsm, "noise_fwd_team_kernel")) return 1;
+            const long long frames = (long long)B * T;
+            noise_fwd_team_kernel<<<(unsigned)((frames + FPB - 1) / FPB), TEAM_BLOCK, tsm, static_cast<cudaStream_t>(stream)>>>(
+                H, noise, y, accumulate, key, offset, voice_offset, T, NB, hop, frames);
+            DDSP_CHECK_LAUNCH("noise_fwd_team_kernel");
+            return 0;
+        }
+    }
     const size_t smem = sizeof(float) * noise_smem_floats(NB, hop);
     if (reserve_smem(noise_fwd_kernel, smem, "noise_fwd_kernel")) return 1;
-    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
     noise_fwd_kernel<<<dim3(T, B), hop / 8, smem, static_cast<cudaStream_t>(stream)>>>(H, noise, y, accumulate, key, offset,
                                                                                       voice_offset, T, NB, hop);
     DDSP_CHECK_LAUNCH("noise_fwd_kernel");
@@ -368,12 +728,24 @@ extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH
                                    uint32_t voice_offset, int B, int T, int NB, int hop, void* stream) {
     if (check_noise_shape("ddsp_noise_backward", B, T, NB, hop)) return 1;
     DDSP_REQUIRE(g && gH, "ddsp_noise_backward: null pointer argument");
+    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
+    if (hop % 16 == 0 && hop / 16 <= TEAM_BLOCK && TEAM_BLOCK % (hop / 16) == 0) {
+        const int FPB = TEAM_BLOCK / (hop / 16);
+        const size_t tsm = sizeof(float) * (size_t)team_bwd_layout(NB, hop).total * FPB;
+        if (tsm <= 200 * 1024) {
+            if (reserve_smem(noise_bwd_team_kernel, tsm, "noise_bwd_team_kernel")) return 1;
+            const long long frames = (long long)B * T;
+            noise_bwd_team_kernel<<<(unsigned)((frames + FPB - 1) / FPB), TEAM_BLOCK, tsm, static_cast<cudaStream_t>(stream)>>>(
+                g, noise, gH, key, offset, voice_offset, T, NB, hop, frames);
+            DDSP_CHECK_LAUNCH("noise_bwd_team_kernel");
+            return 0;
+        }
+    }
     const int nsl = noise_bwd_slices(NB, hop);
     const int threads = noise_tp(NB) / 8 * nsl;
     DDSP_REQUIRE(threads <= 512, "ddsp_noise_backward: NB=%d needs %d threads per frame (max 512)", NB, threads);
     const size_t smem = sizeof(float) * noise_bwd_smem_floats(NB, hop);
     if (reserve_smem(noise_bwd_kernel, smem, "noise_bwd_kernel")) return 1;
-    const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
     noise_bwd_kernel<<<dim3(T, B), threads, smem, static_cast<cudaStream_t>(stream)>>>(g, noise, gH, key, offset, voice_offset,
                                                                                       T, NB, hop, nsl);
     DDSP_CHECK_LAUNCH("noise_bwd_kernel");
