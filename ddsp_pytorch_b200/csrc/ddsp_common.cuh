@@ -29,11 +29,20 @@ void set_error(const char* fmt, ...);
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- frame-rate state of the oscillator (device layout inside the caller's `state` buffer) ----
+// Phase polynomial of one segment in 0.64 fixed-point CYCLES (integer arithmetic wraps mod 1 cycle for free and is
+// exact):  Theta(r) = E + (r+1)*uL + (r+1)^2*du   (mod 2^64),  r = sample index inside the segment.
+struct SegFix {
+    unsigned long long E;    // phase accumulated before the segment
+    unsigned long long uL;   // left frame's increment f0/sample_rate
+    long long du;            // (uR - uL) / (2*hop)
+};
+
 struct OscState {
     float* cn;        // [B,T,K] masked + normalised harmonic amplitudes      (harmonic_oscillator.py:32-33)
     float* csum;      // [B,T]   sum of the masked amplitudes (backward of the normalisation)
     int* kact;        // [B,T]   1 + index of the last unmasked harmonic (K when the frame sum is not > 0)
-    double* phase0;   // [B,T+1] fundamental phase in CYCLES accumulated before each segment, wrapped to [0,1)
+    double* phase0;   // [B,T+1] fundamental phase in CYCLES accumulated before each segment, wrapped to [0,1) (live path)
+    SegFix* seg;      // [B,T+1] the same prefix with the segment's increment pair, fixed point (forward/backward path)
 };
 
 inline OscState carve_osc_state(void* base, int B, int T, int K) {
@@ -46,6 +55,8 @@ inline OscState carve_osc_state(void* base, int B, int T, int K) {
     s.csum = reinterpret_cast<float*>(p);
     p += align_up(sizeof(float) * (size_t)B * T, 256);
     s.kact = reinterpret_cast<int*>(p);
+    p += align_up(sizeof(int) * (size_t)B * T, 256);
+    s.seg = reinterpret_cast<SegFix*>(p);
     return s;
 }
 
@@ -91,6 +102,34 @@ __device__ __forceinline__ PhaseSeed phase_seed(double theta_cycles) {
     c = fma(c, x2, 1.0);
     p.sin1 = (float)(2.0 * s * c);
     p.delta = (float)(-4.0 * s * s);
+    return p;
+}
+
+// Seed from the fixed-point phase: the top 32 bits are the phase in [-0.5, 0.5) cycles as a signed integer; fold to
+// [-0.25, 0.25) by flipping the top bit when bits 31 and 30 differ (theta' = theta -+ pi, sigma = -1); then
+// sin/cos of theta'/2 = pi*t in [-pi/4, pi/4] by fp32 Taylor polynomials (truncation < 3e-9 relative).  No fp64, no MUFU.
+__device__ __forceinline__ PhaseSeed phase_seed_fix(unsigned long long ph) {
+    int h = (int)(ph >> 32);
+    const int flip = (h ^ (h << 1)) & 0x80000000;
+    h ^= flip;
+    PhaseSeed p;
+    p.sigma = __int_as_float(0x3f800000 | flip);
+    const float hf = (float)h;
+    const float x = fmaf(hf, 0x1.921fb6p-31f, hf * -0x1.777a5cp-56f);   // pi * 2^-32 split hi + lo: one rounding
+    const float x2 = x * x;
+    float sp = 2.7557319223985890653e-6f;                //  1/9!
+    sp = fmaf(sp, x2, -1.9841269841269841270e-4f);       // -1/7!
+    sp = fmaf(sp, x2, 8.3333333333333333333e-3f);        //  1/5!
+    sp = fmaf(sp, x2, -1.6666666666666666667e-1f);       // -1/3!
+    const float sv = fmaf(sp * x2, x, x);
+    float cp = -2.7557319223985890653e-7f;               // -1/10!
+    cp = fmaf(cp, x2, 2.4801587301587301587e-5f);        //  1/8!
+    cp = fmaf(cp, x2, -1.3888888888888888889e-3f);       // -1/6!
+    cp = fmaf(cp, x2, 4.1666666666666666667e-2f);        //  1/4!
+    cp = fmaf(cp, x2, -0.5f);
+    const float cv = fmaf(cp, x2, 1.0f);
+    p.sin1 = 2.0f * sv * cv;
+    p.delta = -4.0f * sv * sv;
     return p;
 }
 

@@ -26,7 +26,7 @@ constexpr int PREP_THREADS = 256;
 
 __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
     const float* __restrict__ f0, const float* __restrict__ c, float* __restrict__ cn, float* __restrict__ csum,
-    int* __restrict__ kact, double* __restrict__ phase0, int T, int K, int hop, int sample_rate) {
+    int* __restrict__ kact, double* __restrict__ phase0, SegFix* __restrict__ seg, int T, int K, int hop, int sample_rate) {
     const int b = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = PREP_THREADS / 32;
@@ -67,6 +67,47 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
         __syncthreads();
         if (tid == PREP_THREADS - 1) carry_s = e - floor(e);   // keep the carry small: only the fraction matters
         __syncthreads();
+    }
+
+    // ---- the same prefix in 0.64 fixed point (exact integer scan), with each segment's increment pair --------
+    {
+        __shared__ unsigned long long warp_tot_u[NW];
+        __shared__ unsigned long long carry_u;
+        SegFix* sb = seg + (size_t)b * (T + 1);
+        const double two64 = 18446744073709551616.0;
+        auto ufix = [&](int t) { return (unsigned long long)__double2ll_rn((double)f0b[t] * inv_sr * two64); };
+        const unsigned long long hh = (unsigned long long)(hop / 2);
+        if (tid == 0) carry_u = 0ull - hh * ufix(0);
+        __syncthreads();
+        for (int base = 0; base <= T; base += PREP_THREADS) {
+            const int s = base + tid;                      // segment index, E_s = E_0 + sum_{s'<s} (hop/2)(uL+uR)
+            unsigned long long uL = 0, uR = 0, v = 0;
+            if (s <= T) {
+                uL = ufix(s > 0 ? s - 1 : 0);
+                uR = ufix(s < T ? s : T - 1);
+                v = hh * (uL + uR);
+            }
+            unsigned long long inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long n = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += n;
+            }
+            if (lane == 31) warp_tot_u[warp] = inc;
+            __syncthreads();
+            unsigned long long pre = carry_u;
+            for (int w = 0; w < warp; ++w) pre += warp_tot_u[w];
+            if (s <= T) {
+                SegFix g;
+                g.E = pre + inc - v;                       // exclusive prefix
+                g.uL = uL;
+                g.du = (long long)(uR - uL) / (2ll * hop);
+                sb[s] = g;
+            }
+            __syncthreads();
+            if (tid == PREP_THREADS - 1) carry_u = pre + inc;
+            __syncthreads();
+        }
     }
 
     // ---- mask + normalise each frame: one warp per frame ---------------------------------------
@@ -126,17 +167,56 @@ __device__ __forceinline__ PhaseSeed seed_at(const Segment& g, int r) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// synthesis: grid (T+1, B), hop/R threads, R consecutive samples per thread
+// Per-thread seeds for R consecutive samples r0..r0+R-1 of a segment, packed in pairs for FFMA2/FADD2
+// (fma.rn.f32x2: one issue slot per two FMAs, which is what lets the FMA pipe fill -- profiles/summary_r01c.md).
+// The phase runs in 0.64 fixed point by second differences: two 64-bit adds per sample.
 // ------------------------------------------------------------------------------------------------
-template <int R>
-__global__ void __launch_bounds__(512) osc_synth_kernel(
-    const float* __restrict__ cn, const float* __restrict__ a, const float* __restrict__ f0,
-    const int* __restrict__ kact, const double* __restrict__ phase0, float* __restrict__ y,
-    float* __restrict__ z_save, int accumulate, int T, int K, int hop, double inv_sr) {
-    extern __shared__ __align__(16) float2 amp[];      // (c'_L[k], c'_R[k]-c'_L[k]) for the active harmonics
-    const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-    const Segment g = make_segment(s, T, hop, f0 + (size_t)b * T, phase0 + (size_t)b * (T + 1), inv_sr);
+template <int RP>
+__device__ __forceinline__ void seed_pairs(const SegFix& g, int r0, float2 (&sn)[RP], float2 (&dl)[RP], float2 (&sg)[RP]) {
+    const unsigned long long R1 = (unsigned long long)(r0 + 1);
+    const unsigned long long du = (unsigned long long)g.du;
+    unsigned long long ph = g.E + R1 * g.uL + (R1 * R1) * du;
+    unsigned long long D = g.uL + (2ull * R1 + 1ull) * du;         // Theta(r+1) - Theta(r)
+    const unsigned long long D2 = 2ull * du;
+#pragma unroll
+    for (int j = 0; j < RP; ++j) {
+        const PhaseSeed p0 = phase_seed_fix(ph);
+        ph += D; D += D2;
+        const PhaseSeed p1 = phase_seed_fix(ph);
+        ph += D; D += D2;
+        sn[j] = make_float2(p0.sin1, p1.sin1);
+        dl[j] = make_float2(p0.delta, p1.delta);
+        sg[j] = make_float2(p0.sigma, p1.sigma);
+    }
+}
 
+struct SegGeom {
+    int tL, tR;        // frames interpolated
+    int r_lo, r_hi;    // valid sample range inside the segment
+    long long n0;      // global sample index of r = 0 (negative for s = 0)
+};
+
+__device__ __forceinline__ SegGeom seg_geom(int s, int T, int hop) {
+    SegGeom g;
+    g.tL = s > 0 ? s - 1 : 0;
+    g.tR = s < T ? s : T - 1;
+    g.r_lo = s == 0 ? hop / 2 : 0;
+    g.r_hi = s == T ? hop / 2 : hop;
+    g.n0 = (long long)s * hop - hop / 2;
+    return g;
+}
+
+// ------------------------------------------------------------------------------------------------
+// synthesis: grid (T+1, B), hop/R threads, R consecutive samples per thread (R = 2*RP)
+// ------------------------------------------------------------------------------------------------
+template <int RP>
+__global__ void __launch_bounds__(512) osc_synth_kernel(
+    const float* __restrict__ cn, const float* __restrict__ a, const int* __restrict__ kact,
+    const SegFix* __restrict__ seg, float* __restrict__ y, float* __restrict__ z_save, int accumulate, int T, int K, int hop) {
+    extern __shared__ __align__(16) float4 amp[];      // (c'_L, c'_L, dc', dc') per active harmonic: both halves of an FFMA2 operand
+    constexpr int R = 2 * RP;
+    const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const SegGeom g = seg_geom(s, T, hop);
     const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
     const int kmax = max(kact[fL], kact[fR]);
     const int kpad = (kmax + 1) & ~1;
@@ -144,12 +224,12 @@ __global__ void __launch_bounds__(512) osc_synth_kernel(
         const float* cl = cn + fL * K;
         const float* cr = cn + fR * K;
         for (int k = tid; k < kpad; k += blockDim.x) {
-            float2 v = make_float2(0.f, 0.f);
+            float l = 0.f, d = 0.f;
             if (k < kmax) {
-                const float l = cl[k];
-                v = make_float2(l, cr[k] - l);
+                l = cl[k];
+                d = cr[k] - l;
             }
-            amp[k] = v;
+            amp[k] = make_float4(l, l, d, d);
         }
     }
     __syncthreads();
@@ -157,36 +237,33 @@ __global__ void __launch_bounds__(512) osc_synth_kernel(
     const int r0 = tid * R;
     if (r0 >= g.r_hi || r0 + R <= g.r_lo) return;      // the half-filled first / last segment
 
-    float sn[R], dn[R], dl[R], Pe[R], Po[R], Qe[R], Qo[R];
-    float sg[R];
+    float2 sn[RP], dn[RP], dl[RP], sg[RP], Pe[RP], Po[RP], Qe[RP], Qo[RP];
+    seed_pairs<RP>(seg[(size_t)b * (T + 1) + s], r0, sn, dl, sg);
 #pragma unroll
-    for (int j = 0; j < R; ++j) {
-        const PhaseSeed p = seed_at(g, r0 + j);
-        sn[j] = p.sin1;
-        dn[j] = p.sin1;                                // d_1 = s_1 - s_0, s_0 = 0
-        dl[j] = p.delta;
-        sg[j] = p.sigma;
-        Pe[j] = Po[j] = Qe[j] = Qo[j] = 0.f;
+    for (int j = 0; j < RP; ++j) {
+        dn[j] = sn[j];                                 // d_1 = s_1 - s_0, s_0 = 0
+        Pe[j] = Po[j] = Qe[j] = Qo[j] = make_float2(0.f, 0.f);
     }
 
     // Reinsch recurrence over harmonics m = 1..kmax:  d_{m+1} = d_m + delta*s_m ; s_{m+1} = s_m + d_{m+1}
-    const float4* amp4 = reinterpret_cast<const float4*>(amp);
 #pragma unroll 2
     for (int k = 0; k < kpad; k += 2) {
-        const float4 A = amp4[k >> 1];                 // odd harmonic (x,y), even harmonic (z,w)
+        const float4 A = amp[k], E = amp[k + 1];       // odd harmonic k+1, even harmonic k+2
+        const float2 Ac = make_float2(A.x, A.y), Ad = make_float2(A.z, A.w);
+        const float2 Ec = make_float2(E.x, E.y), Ed = make_float2(E.z, E.w);
 #pragma unroll
-        for (int j = 0; j < R; ++j) {
-            Po[j] = fmaf(A.x, sn[j], Po[j]);
-            Qo[j] = fmaf(A.y, sn[j], Qo[j]);
-            dn[j] = fmaf(dl[j], sn[j], dn[j]);
-            sn[j] += dn[j];
+        for (int j = 0; j < RP; ++j) {
+            Po[j] = __ffma2_rn(Ac, sn[j], Po[j]);
+            Qo[j] = __ffma2_rn(Ad, sn[j], Qo[j]);
+            dn[j] = __ffma2_rn(dl[j], sn[j], dn[j]);
+            sn[j] = __fadd2_rn(sn[j], dn[j]);
         }
 #pragma unroll
-        for (int j = 0; j < R; ++j) {
-            Pe[j] = fmaf(A.z, sn[j], Pe[j]);
-            Qe[j] = fmaf(A.w, sn[j], Qe[j]);
-            dn[j] = fmaf(dl[j], sn[j], dn[j]);
-            sn[j] += dn[j];
+        for (int j = 0; j < RP; ++j) {
+            Pe[j] = __ffma2_rn(Ec, sn[j], Pe[j]);
+            Qe[j] = __ffma2_rn(Ed, sn[j], Qe[j]);
+            dn[j] = __ffma2_rn(dl[j], sn[j], dn[j]);
+            sn[j] = __fadd2_rn(sn[j], dn[j]);
         }
     }
 
@@ -194,27 +271,33 @@ __global__ void __launch_bounds__(512) osc_synth_kernel(
     const float inv_hop = 1.0f / (float)hop;
     float out[R], zs[R];
 #pragma unroll
-    for (int j = 0; j < R; ++j) {
-        const float w = ((float)(r0 + j) + 0.5f) * inv_hop;
-        const float zP = fmaf(sg[j], Po[j], Pe[j]);    // sin(m theta) = sigma^m sin(m theta')
-        const float zQ = fmaf(sg[j], Qo[j], Qe[j]);
-        zs[j] = fmaf(w, zQ, zP);
-        out[j] = fmaf(w, da, aL) * zs[j];
+    for (int j = 0; j < RP; ++j) {
+        const float2 zP = __ffma2_rn(sg[j], Po[j], Pe[j]);     // sin(m theta) = sigma^m sin(m theta')
+        const float2 zQ = __ffma2_rn(sg[j], Qo[j], Qe[j]);
+        const float w0 = ((float)(r0 + 2 * j) + 0.5f) * inv_hop, w1 = ((float)(r0 + 2 * j + 1) + 0.5f) * inv_hop;
+        zs[2 * j] = fmaf(w0, zQ.x, zP.x);
+        zs[2 * j + 1] = fmaf(w1, zQ.y, zP.y);
+        out[2 * j] = fmaf(w0, da, aL) * zs[2 * j];
+        out[2 * j + 1] = fmaf(w1, da, aL) * zs[2 * j + 1];
     }
     const size_t N = (size_t)T * hop;
     float* yp = y + (size_t)b * N + (g.n0 + r0);
     float* zp = z_save ? z_save + (size_t)b * N + (g.n0 + r0) : nullptr;
-    if (R == 4 && ((hop & 7) == 0)) {
-        float4 o = make_float4(out[0], out[1], out[2], out[3]);
-        if (accumulate) {
-            const float4 p = *reinterpret_cast<const float4*>(yp);
-            o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+    if (R % 4 == 0) {                                  // n0 + r0 is then a multiple of 4 (hop % (2R) == 0)
+#pragma unroll
+        for (int j = 0; j < R; j += 4) {
+            float4 o = make_float4(out[j], out[j + 1], out[j + 2], out[j + 3]);
+            if (accumulate) {
+                const float4 p = *reinterpret_cast<const float4*>(yp + j);
+                o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+            }
+            *reinterpret_cast<float4*>(yp + j) = o;
+            if (zp) *reinterpret_cast<float4*>(zp + j) = make_float4(zs[j], zs[j + 1], zs[j + 2], zs[j + 3]);
         }
-        *reinterpret_cast<float4*>(yp) = o;
-        if (zp) *reinterpret_cast<float4*>(zp) = make_float4(zs[0], zs[1], zs[2], zs[3]);
     } else {
 #pragma unroll
         for (int j = 0; j < R; ++j) {
+            if (r0 + j < g.r_lo || r0 + j >= g.r_hi) continue;
             yp[j] = accumulate ? yp[j] + out[j] : out[j];
             if (zp) zp[j] = zs[j];
         }
@@ -231,44 +314,64 @@ __global__ void __launch_bounds__(512) osc_synth_kernel(
 // ------------------------------------------------------------------------------------------------
 constexpr int GRAD_CH = 32;
 
-template <int R>
+template <int RP>
 __global__ void __launch_bounds__(512) osc_grad_kernel(
-    const float* __restrict__ gup, const float* __restrict__ a, const float* __restrict__ f0,
-    const float* __restrict__ z_save, const int* __restrict__ kact, const double* __restrict__ phase0,
-    float2* __restrict__ gseg, float2* __restrict__ gaseg, int T, int K, int hop, double inv_sr) {
+    const float* __restrict__ gup, const float* __restrict__ a, const float* __restrict__ z_save,
+    const int* __restrict__ kact, const SegFix* __restrict__ seg, float2* __restrict__ gseg, float2* __restrict__ gaseg,
+    int T, int K, int hop) {
     extern __shared__ __align__(16) float part[];      // [GRAD_CH][2*NT + 4]
     __shared__ float red[2][16];
+    constexpr int R = 2 * RP;
     const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, NT = blockDim.x;
     const int stride = 2 * NT + 4;
-    const Segment g = make_segment(s, T, hop, f0 + (size_t)b * T, phase0 + (size_t)b * (T + 1), inv_sr);
+    const SegGeom g = seg_geom(s, T, hop);
     const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
     const int kmax = max(kact[fL], kact[fR]);
 
     const int r0 = tid * R;
     const bool live = !(r0 >= g.r_hi || r0 + R <= g.r_lo);
-    float sn[R], dn[R], dl[R], ug[R], uw[R], ugo[R], uwo[R];
+    float2 sn[RP], dn[RP], dl[RP], sg[RP], ug[RP], uw[RP], ugo[RP], uwo[RP];
     float ga0 = 0.f, ga1 = 0.f;
     if (live) {
+        seed_pairs<RP>(seg[(size_t)b * (T + 1) + s], r0, sn, dl, sg);
         const float aL = a[fL], da = a[fR] - aL;
         const float inv_hop = 1.0f / (float)hop;
         const size_t N = (size_t)T * hop;
         const float* gp = gup + (size_t)b * N + (g.n0 + r0);
         const float* zp = z_save + (size_t)b * N + (g.n0 + r0);
+        float gj[R], zj[R];
+        if (R % 4 == 0) {
+#pragma unroll
+            for (int j = 0; j < R; j += 4) {
+                const float4 gv = *reinterpret_cast<const float4*>(gp + j), zv = *reinterpret_cast<const float4*>(zp + j);
+                gj[j] = gv.x; gj[j + 1] = gv.y; gj[j + 2] = gv.z; gj[j + 3] = gv.w;
+                zj[j] = zv.x; zj[j + 1] = zv.y; zj[j + 2] = zv.z; zj[j + 3] = zv.w;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                const bool in = r0 + j >= g.r_lo && r0 + j < g.r_hi;
+                gj[j] = in ? gp[j] : 0.f;
+                zj[j] = in ? zp[j] : 0.f;
+            }
+        }
+        float u1[R], u2[R];
 #pragma unroll
         for (int j = 0; j < R; ++j) {
-            const PhaseSeed p = seed_at(g, r0 + j);
-            sn[j] = p.sin1;
-            dn[j] = p.sin1;
-            dl[j] = p.delta;
             const float w = ((float)(r0 + j) + 0.5f) * inv_hop;
-            const float gj = gp[j];
-            const float gz = gj * zp[j];
+            const float gz = gj[j] * zj[j];
             ga0 += gz;
             ga1 = fmaf(gz, w, ga1);
-            ug[j] = gj * fmaf(w, da, aL);
-            uw[j] = ug[j] * w;
-            ugo[j] = ug[j] * p.sigma;
-            uwo[j] = uw[j] * p.sigma;
+            u1[j] = gj[j] * fmaf(w, da, aL);
+            u2[j] = u1[j] * w;
+        }
+#pragma unroll
+        for (int j = 0; j < RP; ++j) {
+            dn[j] = sn[j];
+            ug[j] = make_float2(u1[2 * j], u1[2 * j + 1]);
+            uw[j] = make_float2(u2[2 * j], u2[2 * j + 1]);
+            ugo[j] = __fmul2_rn(ug[j], sg[j]);
+            uwo[j] = __fmul2_rn(uw[j], sg[j]);
         }
     }
 
@@ -278,23 +381,23 @@ __global__ void __launch_bounds__(512) osc_grad_kernel(
         const int kn2 = (kn + 1) & ~1;
         if (live) {
             for (int kk = 0; kk < kn2; kk += 2) {
-                float p0o = 0.f, p1o = 0.f, p0e = 0.f, p1e = 0.f;
+                float2 p0o = make_float2(0.f, 0.f), p1o = p0o, p0e = p0o, p1e = p0o;
 #pragma unroll
-                for (int j = 0; j < R; ++j) {
-                    p0o = fmaf(ugo[j], sn[j], p0o);
-                    p1o = fmaf(uwo[j], sn[j], p1o);
-                    dn[j] = fmaf(dl[j], sn[j], dn[j]);
-                    sn[j] += dn[j];
+                for (int j = 0; j < RP; ++j) {
+                    p0o = __ffma2_rn(ugo[j], sn[j], p0o);
+                    p1o = __ffma2_rn(uwo[j], sn[j], p1o);
+                    dn[j] = __ffma2_rn(dl[j], sn[j], dn[j]);
+                    sn[j] = __fadd2_rn(sn[j], dn[j]);
                 }
 #pragma unroll
-                for (int j = 0; j < R; ++j) {
-                    p0e = fmaf(ug[j], sn[j], p0e);
-                    p1e = fmaf(uw[j], sn[j], p1e);
-                    dn[j] = fmaf(dl[j], sn[j], dn[j]);
-                    sn[j] += dn[j];
+                for (int j = 0; j < RP; ++j) {
+                    p0e = __ffma2_rn(ug[j], sn[j], p0e);
+                    p1e = __ffma2_rn(uw[j], sn[j], p1e);
+                    dn[j] = __ffma2_rn(dl[j], sn[j], dn[j]);
+                    sn[j] = __fadd2_rn(sn[j], dn[j]);
                 }
-                *reinterpret_cast<float2*>(&part[kk * stride + 2 * tid]) = make_float2(p0o, p1o);
-                *reinterpret_cast<float2*>(&part[(kk + 1) * stride + 2 * tid]) = make_float2(p0e, p1e);
+                *reinterpret_cast<float2*>(&part[kk * stride + 2 * tid]) = make_float2(p0o.x + p0o.y, p1o.x + p1o.y);
+                *reinterpret_cast<float2*>(&part[(kk + 1) * stride + 2 * tid]) = make_float2(p0e.x + p0e.y, p1e.x + p1e.y);
             }
         } else {
             for (int kk = 0; kk < kn2; ++kk)
@@ -377,11 +480,13 @@ __global__ void __launch_bounds__(256) osc_finalize_kernel(
     }
 }
 
-// pick samples-per-thread: hop must split into an even number of threads of R samples, at most 512 threads
+// pick samples-per-thread (even: samples are processed in FFMA2 pairs).  R = 8 or 4 needs the half-filled first / last
+// segment to split on a thread boundary (hop % 2R == 0); R = 2 masks per sample, so any even hop up to 1024 works.
 static int pick_R(int hop, int prefer) {
-    for (int R = prefer; R >= 1; R >>= 1)
-        if (hop % (2 * R) == 0 && hop / R <= 512 && (hop / R >= 32 || R == 1)) return R;
-    for (int R = prefer; R >= 1; R >>= 1)
+    for (int R = prefer; R >= 4; R >>= 1)
+        if (hop % (2 * R) == 0 && hop / R <= 512 && hop / R >= 32) return R;
+    if (hop / 2 <= 512) return 2;
+    for (int R = 4; R <= prefer; R <<= 1)
         if (hop % (2 * R) == 0 && hop / R <= 512) return R;
     return 0;
 }
@@ -403,7 +508,8 @@ using namespace ddsp;
 extern "C" size_t ddsp_osc_state_bytes(int B, int T, int K) {
     if (B < 1 || T < 1 || K < 1) return 0;
     return align_up(sizeof(double) * (size_t)B * (T + 1), 256) + align_up(sizeof(float) * (size_t)B * T * K, 256) +
-           align_up(sizeof(float) * (size_t)B * T, 256) + align_up(sizeof(int) * (size_t)B * T, 256);
+           align_up(sizeof(float) * (size_t)B * T, 256) + align_up(sizeof(int) * (size_t)B * T, 256) +
+           align_up(sizeof(SegFix) * (size_t)B * (T + 1), 256);
 }
 
 extern "C" size_t ddsp_osc_backward_scratch_bytes(int B, int T, int K) {
@@ -416,8 +522,8 @@ extern "C" int ddsp_osc_prepare(const float* f0, const float* c, void* state, in
     if (check_osc_shape("ddsp_osc_prepare", B, T, K, hop, sample_rate)) return 1;
     DDSP_REQUIRE(f0 && c && state, "ddsp_osc_prepare: null pointer argument");
     const OscState S = carve_osc_state(state, B, T, K);
-    osc_prepare_kernel<<<B, PREP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, T, K,
-                                                                                 hop, sample_rate);
+    osc_prepare_kernel<<<B, PREP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, S.seg,
+                                                                                 T, K, hop, sample_rate);
     DDSP_CHECK_LAUNCH("osc_prepare_kernel");
     return 0;
 }
@@ -428,16 +534,23 @@ extern "C" int ddsp_osc_synthesize(const float* f0, const float* a, const void* 
     DDSP_REQUIRE(f0 && a && y && state, "ddsp_osc_synthesize: null pointer argument");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
-    const int R = pick_R(hop, 4);
+    const int R = pick_R(hop, 8);
     const dim3 grid(T + 1, B);
-    const size_t smem = sizeof(float2) * ((K + 1) & ~1);
-    const double inv_sr = 1.0 / (double)sample_rate;
-#define LAUNCH_SYNTH(RR)                                                                                              \
-    osc_synth_kernel<RR><<<grid, hop / RR, smem, st>>>(S.cn, a, f0, S.kact, S.phase0, y, z_save, accumulate, T, K, hop, \
-                                                       inv_sr)
+    const size_t smem = sizeof(float4) * ((K + 1) & ~1);
+#define LAUNCH_SYNTH(RP) \
+    osc_synth_kernel<RP><<<grid, hop / (2 * RP), smem, st>>>(S.cn, a, S.kact, S.seg, y, z_save, accumulate, T, K, hop)
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaSuccess;
+        switch (R) {
+            case 8: e = cudaFuncSetAttribute(osc_synth_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+            case 4: e = cudaFuncSetAttribute(osc_synth_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+            default: e = cudaFuncSetAttribute(osc_synth_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); break;
+        }
+        DDSP_REQUIRE(e == cudaSuccess, "osc_synth_kernel: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e));
+    }
     switch (R) {
-        case 4: LAUNCH_SYNTH(4); break;
-        case 2: LAUNCH_SYNTH(2); break;
+        case 8: LAUNCH_SYNTH(4); break;
+        case 4: LAUNCH_SYNTH(2); break;
         default: LAUNCH_SYNTH(1); break;
     }
 #undef LAUNCH_SYNTH
@@ -452,18 +565,17 @@ extern "C" int ddsp_osc_forward(const float* f0, const float* c, const float* a,
     return ddsp_osc_synthesize(f0, a, state, y, z_save, accumulate, B, T, K, hop, sample_rate, stream);
 }
 
-template <int R>
-static int launch_grad(const float* g, const float* a, const float* f0, const float* z, const OscState& S, float2* gseg,
-                       float2* gaseg, int B, int T, int K, int hop, int sample_rate, cudaStream_t st) {
-    const int NT = hop / R;
+template <int RP>
+static int launch_grad(const float* g, const float* a, const float* z, const OscState& S, float2* gseg, float2* gaseg, int B,
+                       int T, int K, int hop, cudaStream_t st) {
+    const int NT = hop / (2 * RP);
     const size_t smem = sizeof(float) * GRAD_CH * (2 * NT + 4);
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(osc_grad_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(osc_grad_kernel<RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         DDSP_REQUIRE(e == cudaSuccess, "osc_grad_kernel: cannot reserve %zu B of shared memory: %s", smem,
                      cudaGetErrorString(e));
     }
-    osc_grad_kernel<R><<<dim3(T + 1, B), NT, smem, st>>>(g, a, f0, z, S.kact, S.phase0, gseg, gaseg, T, K, hop,
-                                                        1.0 / (double)sample_rate);
+    osc_grad_kernel<RP><<<dim3(T + 1, B), NT, smem, st>>>(g, a, z, S.kact, S.seg, gseg, gaseg, T, K, hop);
     DDSP_CHECK_LAUNCH("osc_grad_kernel");
     return 0;
 }
@@ -481,10 +593,9 @@ extern "C" int ddsp_osc_grad_segments(const float* g, const float* f0, const flo
     float2* gseg = reinterpret_cast<float2*>(scratch);
     float2* gaseg = scratch_gaseg(scratch, B, T, K);
     switch (pick_R(hop, 8)) {
-        case 8: return launch_grad<8>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
-        case 4: return launch_grad<4>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
-        case 2: return launch_grad<2>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
-        default: return launch_grad<1>(g, a, f0, z_save, S, gseg, gaseg, B, T, K, hop, sample_rate, st);
+        case 8: return launch_grad<4>(g, a, z_save, S, gseg, gaseg, B, T, K, hop, st);
+        case 4: return launch_grad<2>(g, a, z_save, S, gseg, gaseg, B, T, K, hop, st);
+        default: return launch_grad<1>(g, a, z_save, S, gseg, gaseg, B, T, K, hop, st);
     }
 }
 
