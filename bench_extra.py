@@ -1,0 +1,175 @@
+#!/usr/bin/env python
+"""Side measurements for the SURVEY.md §8d rows that are not the headline bench line (bench.py keeps the driver
+contract).  One JSON line per workload:
+
+    python bench_extra.py [--workloads mss,reverb,path,rt] [--reps 20]
+
+  mss     cfg 5: MSS loss alone, FFT sizes 2048..64 on 64 x 4 s @ 16 kHz clips, forward + backward
+  reverb  cfg 1' shapes (B=16, N=88064, L=44100) and a large batch (B=256, N=192000, L=48000): fwd + bwd (gx, gir)
+  path    cfg 1': oscillator + noise + reverb + 6-scale MSS, forward + backward through the module API
+  rt      cfg 3: OscillatorBank.live + FilteredNoise + Reverb.live_forward per 2048-sample block, p50/p99 latency
+No CPU fallback: needs the CUDA library and a GPU.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def ev_time(fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    e1.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        return {}
+
+
+def bench_mss(args, dev):
+    from ddsp_pytorch_b200 import ops
+    B, N, n_ffts = 64, 64000, [2048, 1024, 512, 256, 128, 64]
+    g = torch.Generator().manual_seed(1234 + 5)
+    xt = (torch.randn(B, N, generator=g) * 0.1).clamp(-1, 1)
+    xp = (0.5 * xt + torch.randn(B, N, generator=g) * 0.05)
+    xt, xp = xt.to(dev), xp.to(dev).requires_grad_(True)
+
+    def step():
+        xp.grad = None
+        ops.mss_loss(xp, xt, n_ffts).backward()
+
+    ms = ev_time(step, args.reps)
+    fwd_only = ev_time(lambda: ops.mss_loss(xp.detach(), xt, n_ffts), args.reps)
+    samples = B * N
+    flops = (1020 + 510) * samples            # FFT flops fwd (2 signals) + one inverse per pred frame
+    byts = (48 + 52) * samples
+    pk = peaks()
+    return {"workload": "cfg5 MSS alone: 64 x 4 s @ 16 kHz, n_fft 2048..64, fwd+bwd", "ms": ms, "fwd_only_ms": fwd_only,
+            "samples_per_s": samples / (ms * 1e-3), "alg_tflops": flops / (ms * 1e-3) / 1e12,
+            "alg_GBps": byts / (ms * 1e-3) / 1e9, "hbm_peak_GBps": pk.get("hbm_gbs")}
+
+
+def bench_reverb(args, dev):
+    import ddsp_pytorch_b200 as d
+    out = []
+    for (B, N, sr) in ((16, 88064, 44100), (256, 192000, 48000)):
+        conf = d.Config(sample_rate=sr, hop_length=512, n_harmonics=100, n_noise_filters=65)
+        rv = d.Reverb(conf).to(dev)
+        x = (torch.randn(B, N, generator=torch.Generator().manual_seed(3)) * 0.1).to(dev).requires_grad_(True)
+        gy = torch.randn(B, N, generator=torch.Generator().manual_seed(4)).to(dev)
+
+        def step():
+            x.grad = None
+            for p in rv.parameters():
+                p.grad = None
+            rv(x).backward(gy)
+
+        ms = ev_time(step, args.reps)
+        with torch.no_grad():
+            fwd = ev_time(lambda: rv(x), args.reps)
+        byts = 24.0 * B * N                   # 8 fwd + 8 gx + 8 gir bytes per sample
+        out.append({"workload": f"reverb B={B} N={N} L={sr}: fwd+bwd (gx, g_noise, g_decay, g_wet)", "ms": ms, "fwd_only_ms": fwd,
+                    "samples_per_s": B * N / (ms * 1e-3), "alg_GBps": byts / (ms * 1e-3) / 1e9,
+                    "fwd_alg_GBps": 8.0 * B * N / (fwd * 1e-3) / 1e9, "hbm_peak_GBps": peaks().get("hbm_gbs")})
+    return out
+
+
+def bench_path(args, dev):
+    """cfg 1' (shipped config/default.py): decoder tail exactly as decoder.py:129-133 + MSSLoss, fwd+bwd."""
+    import ddsp_pytorch_b200 as d
+    from oracle import ddsp_oracle as O            # input generator only
+    conf = d.SHIPPED
+    B, sr, hop, K, NB = 16, conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters
+    T = 172
+    N = T * hop
+    f0, c, a, H = (t.to(dev) for t in O.synthetic_controls(B, T, K, NB, sr, hop, seed=1234 + 1))
+    target = (torch.randn(B, N, generator=torch.Generator().manual_seed(9)) * 0.1).clamp(-1, 1).to(dev)
+    bank, fn, rv = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=7), d.Reverb(conf).to(dev)
+    loss_fn = d.MSSLoss([2048, 1024, 512, 256, 128, 64]).to(dev)
+    leaves = [c.requires_grad_(True), a.requires_grad_(True), H.requires_grad_(True)]
+
+    def step():
+        for t in leaves + list(rv.parameters()):
+            t.grad = None
+        ctrl = {"f0": f0, "c": c, "a": a, "H": H}
+        dry = bank(ctrl) + fn(ctrl)
+        loss_fn(rv(dry), target).backward()
+
+    ms = ev_time(step, args.reps)
+    return {"workload": f"cfg1' path: B={B} T={T} sr={sr} K={K} NB={NB}: osc + noise + reverb + 6-scale MSS, fwd+bwd",
+            "ms": ms, "samples_per_s": B * N / (ms * 1e-3)}
+
+
+def bench_rt(args, dev):
+    """cfg 3 (rt/synth.py:23, autoencoder.py:26-32): one 2048-sample block = 4 frames, batch 1, live path."""
+    import ddsp_pytorch_b200 as d
+    from oracle import ddsp_oracle as O
+    conf = d.SHIPPED
+    sr, hop, K, NB, T = conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters, 4
+    bank, fn, rv = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=7), d.Reverb(conf).to(dev)
+    ctrls = []
+    for i in range(16):
+        f0, c, a, H = (t.to(dev) for t in O.synthetic_controls(1, T, K, NB, sr, hop, seed=50 + i))
+        ctrls.append({"f0": f0, "c": c, "a": a, "H": H})
+    n_calls = args.rt_calls
+    host_ms, dev_ms = [], []
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_calls)]
+    with torch.no_grad():
+        for i in range(50 + n_calls):
+            ctrl = ctrls[i % len(ctrls)]
+            t0 = time.perf_counter()
+            if i >= 50:
+                evs[i - 50][0].record()
+            y = rv.live_forward(bank.live(ctrl) + fn(ctrl))
+            if i >= 50:
+                evs[i - 50][1].record()
+            out = y.cpu()                                  # decoder.py:147: the JACK callback needs host samples
+            if i >= 50:
+                host_ms.append((time.perf_counter() - t0) * 1e3)
+    torch.cuda.synchronize()
+    dev_ms = [a.elapsed_time(b) for a, b in evs]
+    q = lambda v, p: sorted(v)[min(len(v) - 1, int(p * len(v)))]  # noqa: E731
+    return {"workload": f"cfg3 rt: batch 1, {T * hop}-sample blocks @ {sr} Hz, live osc + noise + live reverb, {n_calls} calls",
+            "deadline_ms": T * hop / sr * 1e3, "host_p50_ms": q(host_ms, 0.5), "host_p99_ms": q(host_ms, 0.99),
+            "host_max_ms": max(host_ms), "device_p50_ms": q(dev_ms, 0.5), "device_p99_ms": q(dev_ms, 0.99),
+            "out_shape": list(out.shape)}
+
+
+def main():
+    p = argparse.ArgumentParser()
+    p.add_argument("--workloads", default="mss,reverb,path,rt")
+    p.add_argument("--reps", type=int, default=20)
+    p.add_argument("--rt-calls", type=int, default=2000)
+    args = p.parse_args()
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench_extra.py needs a CUDA device; there is no CPU fallback")
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    table = {"mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt}
+    for w in args.workloads.split(","):
+        res = table[w](args, dev)
+        for r in (res if isinstance(res, list) else [res]):
+            print(json.dumps(r), flush=True)
+
+
+if __name__ == "__main__":
+    main()
