@@ -158,6 +158,14 @@ int ddsp_mss_backward(const float* gloss, const float* gx_saved, float* gx_out, 
                       void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * The transform underneath the reverb and the spectral loss, on its own: `batch` complex FFTs of
+ * size n (power of two in [8,4096]), interleaved (re,im) fp32 (fp64 = 0) or fp64 (fp64 != 0), in
+ * natural order; inverse != 0 is the unnormalised inverse.  Replaces the cuFFT calls the reference
+ * reaches through torch.fft.rfft/irfft (filtered_noise.py:10,29) and torch.stft (mss_loss.py:23-27).
+ * ------------------------------------------------------------------------------------------ */
+int ddsp_fft_c2c(const void* in, void* out, int n, long long batch, int inverse, int fp64, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Measurement helper: dependent-free FFMA chains, for the measured FP32 roofline denominator.
  * Each thread executes iters*64 FFMAs; out[grid*block] keeps the compiler honest.
  * ------------------------------------------------------------------------------------------ */
