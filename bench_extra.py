@@ -154,6 +154,21 @@ def bench_rt(args, dev):
             "out_shape": list(out.shape)}
 
 
+def bench_fft(args, dev):
+    from ddsp_pytorch_b200 import _lib
+    out = []
+    for n, batch in ((4096, 12032), (2048, 65536), (512, 262144), (64, 2097152)):
+        x = torch.randn(batch, n, dtype=torch.complex64, device=dev)
+        y = torch.empty_like(x)
+        st = torch.cuda.current_stream().cuda_stream
+        ms = ev_time(lambda: _lib.call("ddsp_fft_c2c", x.data_ptr(), y.data_ptr(), n, batch, 0, 0, st), args.reps)
+        ref = ev_time(lambda: torch.fft.fft(x, out=y), args.reps)
+        byts = 16.0 * n * batch
+        out.append({"workload": f"c2c fft n={n} batch={batch} fp32", "ms": ms, "GBps": byts / (ms * 1e-3) / 1e9,
+                    "cufft_ms": ref, "hbm_peak_GBps": peaks().get("hbm_gbs")})
+    return out
+
+
 def main():
     p = argparse.ArgumentParser()
     p.add_argument("--workloads", default="mss,reverb,path,rt")
@@ -164,7 +179,7 @@ def main():
         raise RuntimeError("bench_extra.py needs a CUDA device; there is no CPU fallback")
     dev = torch.device("cuda", 0)
     torch.manual_seed(0)
-    table = {"mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt}
+    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt}
     for w in args.workloads.split(","):
         res = table[w](args, dev)
         for r in (res if isinstance(res, list) else [res]):

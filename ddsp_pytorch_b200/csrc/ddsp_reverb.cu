@@ -5,15 +5,16 @@
 // (non power of two) per call.  Here the causal, truncated convolution y[n] = sum_q ir[q] x[n-q] is a
 // uniformly partitioned overlap-save convolution with P = 2048-sample blocks and 4096-point complex FFTs
 // that live entirely in shared memory:
-//   conv_spectra_kernel   X[b2,i,:] = FFT_4096(x[(i-1)P .. (i+1)P))            one CTA per block i
-//   conv_mac_ifft_kernel  y block i = last P samples of IFFT(sum_j X[i-j] * H[j])
+//   conv_spectra_kernel   X[b2,i,:] = FFT_4096(x[(i-1)P .. (i+1)P))            one CTA per block i (register-tiled FFT)
+//   conv_mac_kernel       Y[b2,i,k] = sum_j H[j,k] X[b2,i-j,k]                  one thread per (bin, voice pair), register ring
+//   conv_ifft_kernel      y block i = last P samples of IFFT(Y[b2,i])
 // Two voices share one complex transform (z = x_a + i x_b): convolution with a REAL kernel is real-linear,
 // so the inverse transform returns y_a + i y_b with no split/merge pass at all.
 // Backward: gx is the same convolution run on the time-reversed gradient; gir is a frequency-domain
 // cross-correlation sum over voices and blocks (conv_gir_kernel -> deterministic two-stage reduction ->
 // conv_gir_finish_kernel); build_impulse has its own forward/backward kernels.
 #include "ddsp_common.cuh"
-#include "ddsp_fft.cuh"
+#include "ddsp_fft8.cuh"
 
 namespace ddsp {
 
@@ -97,17 +98,16 @@ __global__ void __launch_bounds__(1024) reverb_impulse_bwd_kernel(const float* _
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(CONV_THREADS) conv_spectra_kernel(const float* __restrict__ x, float2* __restrict__ S, int B,
                                                                     int N, int nblk, int halves, int reverse, int blk_shift) {
-    extern __shared__ __align__(16) float2 fsm[];
-    float2* a = fsm;
-    float2* b = a + CONV_N2;
-    float2* tw = b + CONV_N2;
+    extern __shared__ __align__(16) float2 fsm[];      // exchange buffer of the register-tiled FFT
     const int i = blockIdx.x, b2 = blockIdx.y, tid = threadIdx.x;
-    fft_fill_twiddles(tw, CONV_N2);
     const int v0 = 2 * b2, v1 = 2 * b2 + 1;
     const float* xa = x + (size_t)v0 * N;
     const float* xb = v1 < B ? x + (size_t)v1 * N : nullptr;
     const long long base = (long long)(i + blk_shift - 1) * CONV_P;
-    for (int m = tid; m < CONV_N2; m += CONV_THREADS) {
+    float2 v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const int m = tid + q * CONV_THREADS;
         const bool on = (m < CONV_P) ? (halves & 1) : (halves & 2);
         const long long n = base + m;
         float re = 0.f, im = 0.f;
@@ -116,53 +116,73 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_spectra_kernel(const float*
             re = xa[idx];
             if (xb) im = xb[idx];
         }
-        a[m] = make_float2(re, im);
+        v[q] = make_float2(re, im);
     }
-    __syncthreads();
-    const float2* out = block_fft<false>(a, b, tw, CONV_N2, tid, CONV_THREADS);
+    fft8_group<CONV_N2, float, false>(v, fsm, tid);
     float2* dst = S + ((size_t)b2 * nblk + i) * CONV_N2;
-    for (int k = tid; k < CONV_N2; k += CONV_THREADS) dst[k] = out[k];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) dst[tid + q * CONV_THREADS] = v[q];
 }
 
-// y block i of voice pair b2: accumulate X[i-j]*H[j] over the IR partitions, inverse FFT, keep the last P.
-__global__ void __launch_bounds__(CONV_THREADS) conv_mac_ifft_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
-                                                                     float* __restrict__ y, int B, int N, int nblk, int np,
-                                                                     int reverse) {
-    extern __shared__ __align__(16) float2 fsm[];
-    float2* a = fsm;
-    float2* b = a + CONV_N2;
-    float2* tw = b + CONV_N2;
-    const int i = blockIdx.x, b2 = blockIdx.y, tid = threadIdx.x;
-    fft_fill_twiddles(tw, CONV_N2);
-    constexpr int PER = CONV_N2 / CONV_THREADS;
-    float2 acc[PER];
+// Y[b2,i,k] (+)= sum_{j<MAC_NP} H[jg+j,k] X[b2,i-jg-j,k]: one thread per (frequency bin, voice pair) walks the blocks
+// in order with the last MAC_NP input spectra of its bin in a register ring (static indices: the walk is unrolled
+// MAC_NP blocks at a time), so every X and H value is read from memory exactly once.
+constexpr int MAC_NP = 24;
+constexpr int MAC_THREADS = 128;
+
+__global__ void __launch_bounds__(MAC_THREADS) conv_mac_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
+                                                               float2* __restrict__ Y, int nblk, int np, int jg, int accumulate) {
+    const int k = blockIdx.x * MAC_THREADS + threadIdx.x, b2 = blockIdx.y;
+    float2 h[MAC_NP], ring[MAC_NP];
 #pragma unroll
-    for (int e = 0; e < PER; ++e) acc[e] = make_float2(0.f, 0.f);
-    const int jmax = i < np - 1 ? i : np - 1;
-    for (int j = 0; j <= jmax; ++j) {
-        const float2* xs = S + ((size_t)b2 * nblk + (i - j)) * CONV_N2;
-        const float2* hs = Hf + (size_t)j * CONV_N2;
+    for (int j = 0; j < MAC_NP; ++j) {
+        h[j] = (jg + j < np) ? Hf[(size_t)(jg + j) * CONV_N2 + k] : make_float2(0.f, 0.f);
+        ring[j] = make_float2(0.f, 0.f);
+    }
+    const float2* xs = S + (size_t)b2 * nblk * CONV_N2 + k;
+    float2* ys = Y + (size_t)b2 * nblk * CONV_N2 + k;
+    for (int i0 = jg; i0 < nblk; i0 += MAC_NP) {
+        float2 nxt[MAC_NP];
 #pragma unroll
-        for (int e = 0; e < PER; ++e) {
-            const int k = tid + e * CONV_THREADS;
-            const float2 p = cmul(xs[k], hs[k]);
-            acc[e].x += p.x;
-            acc[e].y += p.y;
+        for (int u = 0; u < MAC_NP; ++u)
+            nxt[u] = (i0 + u < nblk) ? xs[(size_t)(i0 + u - jg) * CONV_N2] : make_float2(0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < MAC_NP; ++u) {
+            const int i = i0 + u;
+            if (i < nblk) {
+                ring[u] = nxt[u];
+                float2 acc = accumulate ? ys[(size_t)i * CONV_N2] : make_float2(0.f, 0.f);
+#pragma unroll
+                for (int j = 0; j < MAC_NP; ++j) {
+                    const float2 xv = ring[(u - j + MAC_NP) % MAC_NP], hv = h[j];
+                    acc.x = fmaf(xv.x, hv.x, fmaf(-xv.y, hv.y, acc.x));
+                    acc.y = fmaf(xv.x, hv.y, fmaf(xv.y, hv.x, acc.y));
+                }
+                ys[(size_t)i * CONV_N2] = acc;
+            }
         }
     }
+}
+
+// y block i of voice pair b2 = last P samples of IFFT(Y[b2,i]) / 4096
+__global__ void __launch_bounds__(CONV_THREADS) conv_ifft_kernel(const float2* __restrict__ Y, float* __restrict__ y, int B, int N,
+                                                                 int nblk, int reverse) {
+    extern __shared__ __align__(16) float2 fsm[];
+    const int i = blockIdx.x, b2 = blockIdx.y, tid = threadIdx.x;
+    const float2* src = Y + ((size_t)b2 * nblk + i) * CONV_N2;
+    float2 v[8];
 #pragma unroll
-    for (int e = 0; e < PER; ++e) a[tid + e * CONV_THREADS] = acc[e];
-    __syncthreads();
-    const float2* out = block_fft<true>(a, b, tw, CONV_N2, tid, CONV_THREADS);
+    for (int q = 0; q < 8; ++q) v[q] = src[tid + q * CONV_THREADS];
+    fft8_group<CONV_N2, float, true>(v, fsm, tid);
     const float scale = 1.0f / (float)CONV_N2;
     const int v0 = 2 * b2, v1 = 2 * b2 + 1;
-    for (int m = tid; m < CONV_P; m += CONV_THREADS) {
-        const long long n = (long long)i * CONV_P + m;
+#pragma unroll
+    for (int q = 4; q < 8; ++q) {
+        const long long n = (long long)i * CONV_P + (tid + (q - 4) * CONV_THREADS);
         if (n < N) {
-            const float2 v = out[CONV_P + m];
             const long long idx = reverse ? (N - 1 - n) : n;
-            y[(size_t)v0 * N + idx] = v.x * scale;
-            if (v1 < B) y[(size_t)v1 * N + idx] = v.y * scale;
+            y[(size_t)v0 * N + idx] = v[q].x * scale;
+            if (v1 < B) y[(size_t)v1 * N + idx] = v[q].y * scale;
         }
     }
 }
@@ -172,28 +192,34 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_mac_ifft_kernel(const float
 // Thread = frequency bin; CTA (bin tile, voice-pair chunk) walks its voice pairs and blocks, holding one
 // accumulator per IR partition.  Chunk partials are summed in a fixed order by the finish kernel.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
-                                                       float2* __restrict__ part, int B2, int nblk, int np, int jg) {
-    const int k = blockIdx.x * 256 + threadIdx.x;
+__global__ void __launch_bounds__(MAC_THREADS) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
+                                                               float2* __restrict__ part, int B2, int nblk, int np, int jg) {
+    const int k = blockIdx.x * MAC_THREADS + threadIdx.x;
     const int c = blockIdx.y;
     const int per = (B2 + GIR_CHUNKS - 1) / GIR_CHUNKS;
     const int b_lo = c * per, b_hi = min(B2, b_lo + per);
-    float2 acc[GIR_NP];
+    float2 acc[GIR_NP], ring[GIR_NP];
 #pragma unroll
     for (int j = 0; j < GIR_NP; ++j) acc[j] = make_float2(0.f, 0.f);
     for (int b2 = b_lo; b2 < b_hi; ++b2) {
         const float2* xs = Xf + (size_t)b2 * nblk * CONV_N2 + k;
         const float2* gs = Gf + (size_t)b2 * nblk * CONV_N2 + k;
-        for (int i = jg; i < nblk; ++i) {
-            const float2 g = gs[(size_t)i * CONV_N2];
 #pragma unroll
-            for (int j = 0; j < GIR_NP; ++j) {
-                const int src = i - jg - j;
-                if (jg + j < np && src >= 0) {
-                    const float2 xv = xs[(size_t)src * CONV_N2];
-                    const float2 p = cmul_conj(g, xv);            // g * conj(x)
-                    acc[j].x += p.x;
-                    acc[j].y += p.y;
+        for (int j = 0; j < GIR_NP; ++j) ring[j] = make_float2(0.f, 0.f);
+        // ring slot u holds X[i - jg] of the block i = i0 + u being visited; slot (u - j) mod NP then holds X[i - jg - j]
+        for (int i0 = jg; i0 < nblk; i0 += GIR_NP) {
+#pragma unroll
+            for (int u = 0; u < GIR_NP; ++u) {
+                const int i = i0 + u;
+                if (i < nblk) {
+                    ring[u] = xs[(size_t)(i - jg) * CONV_N2];
+                    const float2 g = gs[(size_t)i * CONV_N2];
+#pragma unroll
+                    for (int j = 0; j < GIR_NP; ++j) {
+                        const float2 xv = ring[(u - j + GIR_NP) % GIR_NP];      // g * conj(x)
+                        acc[j].x = fmaf(g.x, xv.x, fmaf(g.y, xv.y, acc[j].x));
+                        acc[j].y = fmaf(g.y, xv.x, fmaf(-g.x, xv.y, acc[j].y));
+                    }
                 }
             }
         }
@@ -206,26 +232,25 @@ __global__ void __launch_bounds__(256) conv_gir_kernel(const float2* __restrict_
 __global__ void __launch_bounds__(CONV_THREADS) conv_gir_finish_kernel(const float2* __restrict__ part, float* __restrict__ gir,
                                                                        int np, int Le) {
     extern __shared__ __align__(16) float2 fsm[];
-    float2* a = fsm;
-    float2* b = a + CONV_N2;
-    float2* tw = b + CONV_N2;
     const int j = blockIdx.x, tid = threadIdx.x;
-    fft_fill_twiddles(tw, CONV_N2);
-    for (int k = tid; k < CONV_N2; k += CONV_THREADS) {
+    float2 v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const int k = tid + q * CONV_THREADS;
         float sx = 0.f, sy = 0.f;
         for (int c = 0; c < GIR_CHUNKS; ++c) {
-            const float2 v = part[((size_t)c * np + j) * CONV_N2 + k];
-            sx += v.x;
-            sy += v.y;
+            const float2 p = part[((size_t)c * np + j) * CONV_N2 + k];
+            sx += p.x;
+            sy += p.y;
         }
-        a[k] = make_float2(sx, sy);
+        v[q] = make_float2(sx, sy);
     }
-    __syncthreads();
-    const float2* out = block_fft<true>(a, b, tw, CONV_N2, tid, CONV_THREADS);
+    fft8_group<CONV_N2, float, true>(v, fsm, tid);
     const float scale = 1.0f / (float)CONV_N2;
-    for (int q = tid; q < CONV_P; q += CONV_THREADS) {
-        const int idx = j * CONV_P + q;
-        if (idx < Le) gir[idx] = out[q].x * scale;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int idx = j * CONV_P + tid + q * CONV_THREADS;
+        if (idx < Le) gir[idx] = v[q].x * scale;
     }
 }
 
@@ -254,22 +279,8 @@ __global__ void __launch_bounds__(256) reverb_live_dot_kernel(const float* __res
     }
 }
 
-static int conv_smem_attr() {
-    static bool done = false;
-    const int bytes = (int)(sizeof(float2) * 3 * CONV_N2);
-    if (!done) {
-        cudaError_t e = cudaFuncSetAttribute(conv_spectra_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_mac_ifft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_gir_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        DDSP_REQUIRE(e == cudaSuccess, "conv: cannot reserve %d B of shared memory: %s", bytes, cudaGetErrorString(e));
-        done = true;
-    }
-    return 0;
-}
-
 static int conv_setup(cudaStream_t st) {
-    if (conv_smem_attr()) return 1;
-    cudaError_t e = fft_ensure_table(st);
+    cudaError_t e = fft8_ensure_tables(st);
     DDSP_REQUIRE(e == cudaSuccess, "conv: twiddle table initialisation failed: %s", cudaGetErrorString(e));
     return 0;
 }
@@ -316,14 +327,19 @@ extern "C" int ddsp_conv_forward(const float* x, const float* ir, float* y, void
     char* base = reinterpret_cast<char*>(scratch);
     float2* Hf = reinterpret_cast<float2*>(base + p.off_H);
     float2* S0 = reinterpret_cast<float2*>(base + p.off_S0);
-    const size_t smem = sizeof(float2) * 3 * CONV_N2;
+    const size_t smem = sizeof(float2) * fft8_smem_elems(CONV_N2);
     const int Le = Lk < N ? Lk : N;
     conv_spectra_kernel<<<dim3(p.np, 1), CONV_THREADS, smem, st>>>(ir, Hf, 1, Le, p.np, 1, 0, 1);
     DDSP_CHECK_LAUNCH("conv_spectra_kernel(ir)");
     conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(x, S0, B, N, p.nblk, 3, 0, 0);
     DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
-    conv_mac_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S0, Hf, y, B, N, p.nblk, p.np, 0);
-    DDSP_CHECK_LAUNCH("conv_mac_ifft_kernel");
+    float2* S1 = reinterpret_cast<float2*>(base + p.off_S1);
+    for (int jg = 0; jg < p.np; jg += MAC_NP) {
+        conv_mac_kernel<<<dim3(CONV_N2 / MAC_THREADS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+        DDSP_CHECK_LAUNCH("conv_mac_kernel");
+    }
+    conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, y, B, N, p.nblk, 0);
+    DDSP_CHECK_LAUNCH("conv_ifft_kernel");
     return 0;
 }
 
@@ -339,15 +355,19 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
     float2* S0 = reinterpret_cast<float2*>(base + p.off_S0);
     float2* S1 = reinterpret_cast<float2*>(base + p.off_S1);
     float2* part = reinterpret_cast<float2*>(base + p.off_part);
-    const size_t smem = sizeof(float2) * 3 * CONV_N2;
+    const size_t smem = sizeof(float2) * fft8_smem_elems(CONV_N2);
     const int Le = Lk < N ? Lk : N;
     if (gx) {      // gx = flip(conv(flip(g), ir))
         conv_spectra_kernel<<<dim3(p.np, 1), CONV_THREADS, smem, st>>>(ir, Hf, 1, Le, p.np, 1, 0, 1);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(ir)");
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S0, B, N, p.nblk, 3, 1, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(flip g)");
-        conv_mac_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S0, Hf, gx, B, N, p.nblk, p.np, 1);
-        DDSP_CHECK_LAUNCH("conv_mac_ifft_kernel(gx)");
+        for (int jg = 0; jg < p.np; jg += MAC_NP) {
+            conv_mac_kernel<<<dim3(CONV_N2 / MAC_THREADS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+            DDSP_CHECK_LAUNCH("conv_mac_kernel(gx)");
+        }
+        conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, gx, B, N, p.nblk, 1);
+        DDSP_CHECK_LAUNCH("conv_ifft_kernel(gx)");
     }
     if (gir) {
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(x, S0, B, N, p.nblk, 3, 0, 0);
@@ -355,7 +375,7 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S1, B, N, p.nblk, 2, 0, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(g tail)");
         for (int jg = 0; jg < p.np; jg += GIR_NP) {
-            conv_gir_kernel<<<dim3(CONV_N2 / 256, GIR_CHUNKS), 256, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
+            conv_gir_kernel<<<dim3(CONV_N2 / MAC_THREADS, GIR_CHUNKS), MAC_THREADS, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
             DDSP_CHECK_LAUNCH("conv_gir_kernel");
         }
         cudaError_t e = cudaMemsetAsync(gir, 0, sizeof(float) * (size_t)Lk, st);
