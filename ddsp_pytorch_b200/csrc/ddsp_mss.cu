@@ -13,6 +13,7 @@
 // backward is one multiply by the upstream scalar).
 #include "ddsp_common.cuh"
 #include "ddsp_fft.cuh"
+#include "ddsp_fft8.cuh"
 
 namespace ddsp {
 
@@ -174,6 +175,185 @@ __global__ void __launch_bounds__(MSS_THREADS) mss_scale_kernel(const float* __r
     }
 }
 
+// ================================================================================================
+// Fast path (n_fft >= 8): register-tiled FFTs (ddsp_fft8.cuh).  A group of n/8 threads owns one PAIR of
+// consecutive frames of a voice; thread t holds elements m = t + q*n/8 (q = 0..7) of the windowed pair, bins
+// k = t + q*n/8 (q = 0..3, plus n/2 on thread 0) of its spectra, and the same elements of the gradient frame.
+// The window values a thread needs are the same for every frame, so they live in registers.
+// ================================================================================================
+template <int N>
+struct MssFast {
+    static constexpr int T8 = N / 8;                              // threads per frame pair
+    static constexpr int THREADS = T8 > 128 ? T8 : 128;
+    static constexpr int G = THREADS / T8;                        // frame pairs in flight per CTA
+    static constexpr int ITERS = N >= 1024 ? 2 : 4;               // frame pairs per group, sequentially
+    static constexpr size_t group_bytes = sizeof(double2) * fft8_smem_elems(N);
+    static constexpr size_t smem = group_bytes * G;
+};
+
+template <int N>
+__global__ void __launch_bounds__(MssFast<N>::THREADS) mss_fast_kernel(const float* __restrict__ xp, const float* __restrict__ xt,
+                                                                      double* __restrict__ loss, double* __restrict__ terms,
+                                                                      float* __restrict__ gx, const float* __restrict__ window,
+                                                                      int Nsig, int hop, int F, double inv_count, double alpha_d,
+                                                                      float eps) {
+    using P = MssFast<N>;
+    constexpr int T8 = P::T8, half = N / 2;
+    extern __shared__ __align__(16) unsigned char mss_raw[];
+    __shared__ double red[2][P::THREADS / 32];
+    const int tid = threadIdx.x, grp = tid / T8, t = tid % T8;
+    const int b = blockIdx.y;
+    double2* smd = reinterpret_cast<double2*>(mss_raw + (size_t)grp * P::group_bytes);
+    float2* smf = reinterpret_cast<float2*>(smd);
+    const float* xpb = xp + (size_t)b * Nsig;
+    const float* xtb = xt + (size_t)b * Nsig;
+    float* gxb = gx ? gx + (size_t)b * Nsig : nullptr;
+
+    // the reference's window is the fp32 buffer of its Spectrogram module (mss_loss.py:23); use the caller's copy when
+    // given so both sides window with the same values, else the periodic Hann
+    float win[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const int m = t + q * T8;
+        win[q] = window ? window[m] : 0.5f - 0.5f * (float)cospi(2.0 * (double)m / (double)N);
+    }
+    const float w_lin = (float)inv_count, w_log = (float)(alpha_d * inv_count);
+    const float inv_ln2 = 1.4426950408889634f;
+    double acc_lin = 0.0, acc_log = 0.0;
+
+    for (int it = 0; it < P::ITERS; ++it) {
+        const int fa = 2 * ((blockIdx.x * P::ITERS + it) * P::G + grp), fb = fa + 1;
+        const bool live_a = fa < F, live_b = fb < F;   // dead groups still walk through every barrier
+        const int pa = fa * hop - half, pb = fb * hop - half;
+        int ia[8], ib[8];                              // reflect-padded sample indices of the two frames
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            ia[q] = reflect_index(pa + t + q * T8, Nsig);
+            ib[q] = reflect_index(pb + t + q * T8, Nsig);
+        }
+
+        // ---- true frames: power spectra of bins k = t + q*T8 (q < 4) and n/2, kept in registers ----------
+        float St[2][5];
+        {
+            float2 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+                v[q] = make_float2(live_a ? win[q] * xtb[ia[q]] : 0.f, live_b ? win[q] * xtb[ib[q]] : 0.f);
+            fft8_group<N, float, false>(v, smf, t);
+            fft8_sync<N>();
+#pragma unroll
+            for (int q = 0; q < 8; ++q) smf[fft8_pad<float>(t + q * T8)] = v[q];
+            fft8_sync<N>();
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+                const int k = q < 4 ? t + q * T8 : half;
+                const float2 zk = q < 4 ? v[q] : smf[fft8_pad<float>(half)];
+                const float2 zn = smf[fft8_pad<float>((N - k) & (N - 1))];
+                float2 xa, xb;
+                split_pair(zk, zn, xa, xb);
+                St[0][q] = xa.x * xa.x + xa.y * xa.y;
+                St[1][q] = xb.x * xb.x + xb.y * xb.y;
+            }
+            fft8_sync<N>();
+        }
+
+        // ---- predicted frames in fp64: their small bins decide d log2(S+eps)/dx ---------------------------
+        double2 vd[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            vd[q] = make_double2(live_a ? (double)win[q] * (double)xpb[ia[q]] : 0.0, live_b ? (double)win[q] * (double)xpb[ib[q]] : 0.0);
+        fft8_group<N, double, false>(vd, smd, t);
+        fft8_sync<N>();
+#pragma unroll
+        for (int q = 0; q < 8; ++q) smd[fft8_pad<double>(t + q * T8)] = vd[q];
+        fft8_sync<N>();
+        float2 Yk[5], Yn[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            Yk[q] = Yn[q] = make_float2(0.f, 0.f);
+            if (q == 4 && t != 0) continue;            // bin n/2 belongs to thread 0
+            const int k = q < 4 ? t + q * T8 : half;
+            const double2 zk = q < 4 ? vd[q] : smd[fft8_pad<double>(half)];
+            const double2 zn = smd[fft8_pad<double>((N - k) & (N - 1))];
+            const double xr[2] = {0.5 * (zk.x + zn.x), 0.5 * (zk.y + zn.y)};
+            const double xi[2] = {0.5 * (zk.y - zn.y), -0.5 * (zk.x - zn.x)};
+            float2 G[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                G[e] = make_float2(0.f, 0.f);
+                if (e == 0 ? live_a : live_b) {
+                    const float sp = (float)(xr[e] * xr[e] + xi[e] * xi[e]), st = St[e][q];          // power=2 spectrogram
+                    const float dl = sp - st;
+                    const float dq = log2f(sp + eps) - log2f(st + eps);
+                    acc_lin += (double)fabsf(dl);
+                    acc_log += (double)fabsf(dq);
+                    const float sl = (dl > 0.f) - (dl < 0.f), sq = (dq > 0.f) - (dq < 0.f);
+                    const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);               // d loss / d S_pred
+                    G[e] = make_float2(2.f * (float)xr[e] * gs_, 2.f * (float)xi[e] * gs_);          // d loss / d X_pred
+                }
+            }
+            // x-gradient of a frame = w * Re sum_{k<=n/2} G_k e^{+i 2 pi jk/n}: Hermitian-extend G (halved off the
+            // edges) so the inverse transform is real, and carry the two frames as real / imaginary part
+            if (k == 0 || k == half) {
+                Yk[q] = make_float2(G[0].x, G[1].x);
+            } else {
+                Yk[q] = make_float2(0.5f * (G[0].x - G[1].y), 0.5f * (G[0].y + G[1].x));
+                Yn[q] = make_float2(0.5f * (G[0].x + G[1].y), 0.5f * (G[1].x - G[0].y));
+            }
+        }
+        fft8_sync<N>();                                // everyone has read the fp64 spectra
+        if (gxb) {
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+                if (q == 4 && t != 0) continue;
+                const int k = q < 4 ? t + q * T8 : half;
+                smf[fft8_pad<float>(k)] = Yk[q];
+                if (k != 0 && k != half) smf[fft8_pad<float>(N - k)] = Yn[q];
+            }
+            fft8_sync<N>();
+            float2 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = smf[fft8_pad<float>(t + q * T8)];
+            fft8_sync<N>();
+            fft8_group<N, float, true>(v, smf, t);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                if (live_a) atomicAdd(&gxb[ia[q]], v[q].x * win[q]);
+                if (live_b) atomicAdd(&gxb[ib[q]], v[q].y * win[q]);
+            }
+            fft8_sync<N>();                            // the inverse transform's last exchange is read
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        acc_lin += __shfl_xor_sync(0xffffffffu, acc_lin, o);
+        acc_log += __shfl_xor_sync(0xffffffffu, acc_log, o);
+    }
+    if ((tid & 31) == 0) { red[0][tid >> 5] = acc_lin; red[1][tid >> 5] = acc_log; }
+    __syncthreads();
+    if (tid == 0) {
+        double l = 0.0, q = 0.0;
+        for (int w = 0; w < P::THREADS / 32; ++w) { l += red[0][w]; q += red[1][w]; }
+        atomicAdd(&terms[0], l);
+        atomicAdd(&terms[1], q);
+        atomicAdd(loss, (l + alpha_d * q) * inv_count);
+    }
+}
+
+template <int N>
+static int launch_mss_fast(const float* xp, const float* xt, double* loss, double* terms, float* gx, const float* window, int B,
+                           int Nsig, int hop, int F, double inv_count, double alpha_d, float eps, cudaStream_t st) {
+    using P = MssFast<N>;
+    if (P::smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(mss_fast_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P::smem);
+        DDSP_REQUIRE(e == cudaSuccess, "mss_fast_kernel: cannot reserve %zu B of shared memory: %s", (size_t)P::smem, cudaGetErrorString(e));
+    }
+    const int per_cta = 2 * P::G * P::ITERS;
+    mss_fast_kernel<N><<<dim3((F + per_cta - 1) / per_cta, B), P::THREADS, P::smem, st>>>(xp, xt, loss, terms, gx, window, Nsig, hop, F,
+                                                                                          inv_count, alpha_d, eps);
+    DDSP_CHECK_LAUNCH("mss_fast_kernel");
+    return 0;
+}
+
 __global__ void scale_by_scalar_kernel(const float* __restrict__ in, const float* __restrict__ s, float* __restrict__ out, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = in[i] * s[0];
@@ -203,6 +383,7 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
     }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     cudaError_t e = fft_ensure_table(st);
+    if (e == cudaSuccess) e = fft8_ensure_tables(st);
     DDSP_REQUIRE(e == cudaSuccess, "ddsp_mss_forward: twiddle table initialisation failed: %s", cudaGetErrorString(e));
     e = cudaMemsetAsync(loss_terms, 0, sizeof(double) * (1 + 2 * (size_t)n_scales), st);
     if (e == cudaSuccess && gx) e = cudaMemsetAsync(gx, 0, sizeof(float) * (size_t)B * N, st);
@@ -210,7 +391,20 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
     for (int s = 0; s < n_scales; ++s) {
         const int n = n_ffts_host[s], hop = hops_host[s];
         const int F = 1 + N / hop;
-        const MssGeom g = mss_geom(n);
+        const double cnt = (double)ddsp_mss_count(B, N, n, hop);
+        const float* wptr = windows_host ? windows_host[s] : nullptr;
+        double* terms = loss_terms + 1 + 2 * s;
+        int rc = -1;
+        switch (n) {
+#define MSS_CASE(NN) case NN: rc = launch_mss_fast<NN>(x_pred, x_true, loss_terms, terms, gx, wptr, B, N, hop, F, 1.0 / cnt, (double)alpha, eps, st); break
+            MSS_CASE(8); MSS_CASE(16); MSS_CASE(32); MSS_CASE(64); MSS_CASE(128); MSS_CASE(256);
+            MSS_CASE(512); MSS_CASE(1024); MSS_CASE(2048); MSS_CASE(4096);
+#undef MSS_CASE
+            default: break;
+        }
+        if (rc == 0) continue;
+        if (rc > 0) return rc;
+        const MssGeom g = mss_geom(n);                  // n = 4: the generic shared-memory kernel
         const size_t smem = mss_smem_bytes(n);
         if (smem > 48 * 1024) {
             e = cudaFuncSetAttribute(mss_scale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
