@@ -23,6 +23,7 @@ namespace ddsp {
 // frame-rate preparation: one CTA per voice
 // ------------------------------------------------------------------------------------------------
 constexpr int PREP_THREADS = 256;
+constexpr int PREP_TILE = 32;          // frames normalised per CTA
 
 __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
     const float* __restrict__ f0, const float* __restrict__ c, float* __restrict__ cn, float* __restrict__ csum,
@@ -32,10 +33,43 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
     constexpr int NW = PREP_THREADS / 32;
     __shared__ double warp_tot[NW];
     __shared__ double carry_s;
+    const float* f0b = f0 + (size_t)b * T;
+
+    // blockIdx.y >= 1: mask + normalise a tile of PREP_TILE frames, one warp per frame (harmonic_oscillator.py:31-33);
+    // blockIdx.y == 0: the two phase scans of the voice
+    if (blockIdx.y > 0) {
+        const float nyq = (float)(sample_rate / 2);        // integer floor, compared as float (:31)
+        const int t_lo = (blockIdx.y - 1) * PREP_TILE, t_hi = min(T, t_lo + PREP_TILE);
+        for (int t = t_lo + warp; t < t_hi; t += NW) {
+            const float f = f0b[t];
+            const float* cr = c + ((size_t)b * T + t) * K;
+            float* cnr = cn + ((size_t)b * T + t) * K;
+            float sum = 0.f;
+            int last = 0;
+            for (int k = lane; k < K; k += 32) {
+                const bool masked = (float)(k + 1) * f > nyq;
+                const float v = masked ? 0.f : cr[k];
+                sum += v;
+                if (!masked) last = k + 1;
+            }
+            sum = warp_sum(sum);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
+            if (!(sum > 0.f)) last = K;                     // 0/0 or NaN frame: keep every harmonic so NaN propagates like :33
+            for (int k = lane; k < K; k += 32) {
+                const bool masked = (float)(k + 1) * f > nyq;
+                cnr[k] = (masked ? 0.f : cr[k]) / sum;
+            }
+            if (lane == 0) {
+                csum[(size_t)b * T + t] = sum;
+                kact[(size_t)b * T + t] = last;
+            }
+        }
+        return;
+    }
 
     // ---- phase prefix over segments, fp64, in cycles -------------------------------------------
     // E_0 = -(hop/2) u_0 ; E_{s+1} = E_s + hop*(u_{max(s-1,0)} + u_s)/2          (u = f0 / sample_rate)
-    const float* f0b = f0 + (size_t)b * T;
     double* Eb = phase0 + (size_t)b * (T + 1);
     const double inv_sr = 1.0 / (double)sample_rate;
     if (tid == 0) {
@@ -107,34 +141,6 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
             __syncthreads();
             if (tid == PREP_THREADS - 1) carry_u = pre + inc;
             __syncthreads();
-        }
-    }
-
-    // ---- mask + normalise each frame: one warp per frame ---------------------------------------
-    const float nyq = (float)(sample_rate / 2);        // integer floor, compared as float (:31)
-    for (int t = warp; t < T; t += NW) {
-        const float f = f0b[t];
-        const float* cr = c + ((size_t)b * T + t) * K;
-        float* cnr = cn + ((size_t)b * T + t) * K;
-        float sum = 0.f;
-        int last = 0;
-        for (int k = lane; k < K; k += 32) {
-            const bool masked = (float)(k + 1) * f > nyq;
-            const float v = masked ? 0.f : cr[k];
-            sum += v;
-            if (!masked) last = k + 1;
-        }
-        sum = warp_sum(sum);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
-        if (!(sum > 0.f)) last = K;                     // 0/0 or NaN frame: keep every harmonic so NaN propagates like :33
-        for (int k = lane; k < K; k += 32) {
-            const bool masked = (float)(k + 1) * f > nyq;
-            cnr[k] = (masked ? 0.f : cr[k]) / sum;
-        }
-        if (lane == 0) {
-            csum[(size_t)b * T + t] = sum;
-            kact[(size_t)b * T + t] = last;
         }
     }
 }
@@ -522,7 +528,7 @@ extern "C" int ddsp_osc_prepare(const float* f0, const float* c, void* state, in
     if (check_osc_shape("ddsp_osc_prepare", B, T, K, hop, sample_rate)) return 1;
     DDSP_REQUIRE(f0 && c && state, "ddsp_osc_prepare: null pointer argument");
     const OscState S = carve_osc_state(state, B, T, K);
-    osc_prepare_kernel<<<B, PREP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, S.seg,
+    osc_prepare_kernel<<<dim3(B, 1 + (T + PREP_TILE - 1) / PREP_TILE), PREP_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(f0, c, S.cn, S.csum, S.kact, S.phase0, S.seg,
                                                                                  T, K, hop, sample_rate);
     DDSP_CHECK_LAUNCH("osc_prepare_kernel");
     return 0;

@@ -22,7 +22,8 @@ constexpr int CONV_P = 2048;            // new samples per block
 constexpr int CONV_N2 = 2 * CONV_P;     // FFT size
 constexpr int CONV_THREADS = 512;
 constexpr int GIR_CHUNKS = 32;          // partial sums over voice pairs kept apart for a fixed-order reduction
-constexpr int GIR_NP = 24;              // IR partitions handled per pass of the gir kernel
+constexpr int GIR_NP = 24;
+constexpr int GIR_PF = 6;              // prefetch depth of the gir walk (divides GIR_NP)              // IR partitions handled per pass of the gir kernel
 
 struct ConvPlan {
     int B2, nblk, np;
@@ -65,16 +66,31 @@ __global__ void __launch_bounds__(1024) reverb_impulse_bwd_kernel(const float* _
     __shared__ double red[2][32];
     const float sp = softplus_f(-decay[0]), sg = sigmoid_f(wet[0]), sgd = sigmoid_f(-decay[0]);
     double aw = 0.0, ad = 0.0;
-    for (int i = threadIdx.x; i < L; i += blockDim.x) {
-        float gn = 0.f;
-        if (i > 0) {                                      // ir[0] is overwritten with 1 (:28): no gradient
-            const float env = expf(-sp * t[i] * 500.f), g = gir[i];
-            gn = g * env * sg;
-            const float gne = g * noise[i] * env;
-            aw += (double)(gne * sg * (1.f - sg));
-            ad += (double)(gne * sg * t[i] * 500.f * sgd);
+    constexpr int U = 8;                                  // loads of U strides are issued together (one CTA: latency bound)
+    for (int i0 = threadIdx.x; i0 < L; i0 += U * blockDim.x) {
+        float tv[U], gv[U], nv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = i0 + u * blockDim.x;
+            const bool in = i < L;
+            tv[u] = in ? t[i] : 0.f;
+            gv[u] = in ? gir[i] : 0.f;
+            nv[u] = in ? noise[i] : 0.f;
         }
-        gnoise[i] = gn;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int i = i0 + u * blockDim.x;
+            if (i >= L) continue;
+            float gn = 0.f;
+            if (i > 0) {                                  // ir[0] is overwritten with 1 (:28): no gradient
+                const float env = expf(-sp * tv[u] * 500.f), g = gv[u];
+                gn = g * env * sg;
+                const float gne = g * nv[u] * env;
+                aw += (double)(gne * sg * (1.f - sg));
+                ad += (double)(gne * sg * tv[u] * 500.f * sgd);
+            }
+            gnoise[i] = gn;
+        }
     }
     for (int o = 16; o > 0; o >>= 1) {
         aw += __shfl_xor_sync(0xffffffffu, aw, o);
@@ -195,8 +211,8 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_ifft_kernel(const float2* _
 __global__ void __launch_bounds__(MAC_THREADS) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
                                                                float2* __restrict__ part, int B2, int nblk, int np, int jg) {
     const int k = blockIdx.x * MAC_THREADS + threadIdx.x;
-    const int c = blockIdx.y;
-    const int per = (B2 + GIR_CHUNKS - 1) / GIR_CHUNKS;
+    const int c = blockIdx.y, nchunks = gridDim.y;
+    const int per = (B2 + nchunks - 1) / nchunks;
     const int b_lo = c * per, b_hi = min(B2, b_lo + per);
     float2 acc[GIR_NP], ring[GIR_NP];
 #pragma unroll
@@ -209,16 +225,26 @@ __global__ void __launch_bounds__(MAC_THREADS) conv_gir_kernel(const float2* __r
         // ring slot u holds X[i - jg] of the block i = i0 + u being visited; slot (u - j) mod NP then holds X[i - jg - j]
         for (int i0 = jg; i0 < nblk; i0 += GIR_NP) {
 #pragma unroll
-            for (int u = 0; u < GIR_NP; ++u) {
-                const int i = i0 + u;
-                if (i < nblk) {
-                    ring[u] = xs[(size_t)(i - jg) * CONV_N2];
-                    const float2 g = gs[(size_t)i * CONV_N2];
+            for (int u0 = 0; u0 < GIR_NP; u0 += GIR_PF) {
+                float2 nx[GIR_PF], ng[GIR_PF];          // loads of GIR_PF blocks in flight together
 #pragma unroll
-                    for (int j = 0; j < GIR_NP; ++j) {
-                        const float2 xv = ring[(u - j + GIR_NP) % GIR_NP];      // g * conj(x)
-                        acc[j].x = fmaf(g.x, xv.x, fmaf(g.y, xv.y, acc[j].x));
-                        acc[j].y = fmaf(g.y, xv.x, fmaf(-g.x, xv.y, acc[j].y));
+                for (int v = 0; v < GIR_PF; ++v) {
+                    const int i = i0 + u0 + v;
+                    nx[v] = i < nblk ? xs[(size_t)(i - jg) * CONV_N2] : make_float2(0.f, 0.f);
+                    ng[v] = i < nblk ? gs[(size_t)i * CONV_N2] : make_float2(0.f, 0.f);
+                }
+#pragma unroll
+                for (int v = 0; v < GIR_PF; ++v) {
+                    const int u = u0 + v;
+                    if (i0 + u < nblk) {
+                        ring[u] = nx[v];
+                        const float2 g = ng[v];
+#pragma unroll
+                        for (int j = 0; j < GIR_NP; ++j) {
+                            const float2 xv = ring[(u - j + GIR_NP) % GIR_NP];      // g * conj(x)
+                            acc[j].x = fmaf(g.x, xv.x, fmaf(g.y, xv.y, acc[j].x));
+                            acc[j].y = fmaf(g.y, xv.x, fmaf(-g.x, xv.y, acc[j].y));
+                        }
                     }
                 }
             }
@@ -230,7 +256,7 @@ __global__ void __launch_bounds__(MAC_THREADS) conv_gir_kernel(const float2* __r
 }
 
 __global__ void __launch_bounds__(CONV_THREADS) conv_gir_finish_kernel(const float2* __restrict__ part, float* __restrict__ gir,
-                                                                       int np, int Le) {
+                                                                       int np, int Le, int nchunks) {
     extern __shared__ __align__(16) float2 fsm[];
     const int j = blockIdx.x, tid = threadIdx.x;
     float2 v[8];
@@ -238,7 +264,8 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_gir_finish_kernel(const flo
     for (int q = 0; q < 8; ++q) {
         const int k = tid + q * CONV_THREADS;
         float sx = 0.f, sy = 0.f;
-        for (int c = 0; c < GIR_CHUNKS; ++c) {
+#pragma unroll 4
+        for (int c = 0; c < nchunks; ++c) {
             const float2 p = part[((size_t)c * np + j) * CONV_N2 + k];
             sx += p.x;
             sy += p.y;
@@ -374,13 +401,14 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S1, B, N, p.nblk, 2, 0, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(g tail)");
+        const int nchunks = p.B2 < GIR_CHUNKS ? p.B2 : GIR_CHUNKS;
         for (int jg = 0; jg < p.np; jg += GIR_NP) {
-            conv_gir_kernel<<<dim3(CONV_N2 / MAC_THREADS, GIR_CHUNKS), MAC_THREADS, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
+            conv_gir_kernel<<<dim3(CONV_N2 / MAC_THREADS, nchunks), MAC_THREADS, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
             DDSP_CHECK_LAUNCH("conv_gir_kernel");
         }
         cudaError_t e = cudaMemsetAsync(gir, 0, sizeof(float) * (size_t)Lk, st);
         DDSP_REQUIRE(e == cudaSuccess, "ddsp_conv_backward: memset failed: %s", cudaGetErrorString(e));
-        conv_gir_finish_kernel<<<p.np, CONV_THREADS, smem, st>>>(part, gir, p.np, Le);
+        conv_gir_finish_kernel<<<p.np, CONV_THREADS, smem, st>>>(part, gir, p.np, Le, nchunks);
         DDSP_CHECK_LAUNCH("conv_gir_finish_kernel");
     }
     return 0;
