@@ -44,6 +44,7 @@ def parse_args():
     p.add_argument("--cpu-voices", type=int, default=2, help="voices in the bounded CPU sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--e2e-chunk", type=int, default=64, help="voices per chunk of the host pipeline")
     return p.parse_args()
 
 
@@ -262,20 +263,16 @@ def run_b200(args):
     # ---- end to end through the module API with host buffers -----------------------------------
     e2e = None
     if not args.no_e2e:
-        bank, fnoise = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=seed, voice_offset=voff)
+        from ddsp_pytorch_b200.host_pipeline import HostSynthPipeline
+        pipe = HostSynthPipeline(conf, dev, chunk_voices=args.e2e_chunk, seed=seed, voice_offset=voff)
         outs = [torch.empty(s, dtype=torch.float32).pin_memory() for s in ((Bl, T, K), (Bl, T, 1), (Bl, T, NB))]
         h2d = sum(t.numel() * 4 for t in host)
         d2h = sum(t.numel() * 4 for t in outs)
 
         def e2e_step():
-            f0d, cd, ad, Hd, gd = (t.to(dev, non_blocking=True) for t in host)
-            cd.requires_grad_(True); ad.requires_grad_(True); Hd.requires_grad_(True)
-            ctrl = {"f0": f0d, "c": cd, "a": ad, "H": Hd}
-            y = bank(ctrl) + fnoise(ctrl)                     # decoder.py:129-132
-            y.backward(gd)
-            for o, t in zip(outs, (cd.grad, ad.grad, Hd.grad)):
-                o.copy_(t, non_blocking=True)
-            torch.cuda.current_stream().synchronize()         # the host now owns the gradients
+            # public API call: pinned host controls + upstream gradient in, pinned host gradients out; returns once
+            # the host owns them (copies and kernels of different voice chunks overlap on three streams)
+            pipe.step(*host, *outs)
 
         for _ in range(max(args.warmup, 3)):
             e2e_step()
@@ -288,7 +285,8 @@ def run_b200(args):
         ems = max_over_ranks(e0.elapsed_time(e1))
         e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                "d2h_bytes_per_step": d2h * world, "ms_per_step": ems / args.steps,
-               "path": "pinned host f0,c,a,H,g -> OscillatorBank + FilteredNoise modules (+ torch add) -> backward -> grads to pinned host"}
+               "path": f"HostSynthPipeline.step: pinned host f0,c,a,H,g -> {args.e2e_chunk}-voice chunks on copy-in / compute / copy-out streams "
+                       "(ops.filtered_noise + ops.oscillator_bank, backward) -> grads in pinned host memory"}
 
     # ---- per-kernel device times (rank 0's shard) and the roofline of the dominant kernel -------
     lib = _lib.load()
