@@ -209,13 +209,14 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     sh = shapes(args)
-    assert sh["B"] % world == 0, "voices must divide over ranks"
-    Bl = sh["B"] // world
+    from ddsp_pytorch_b200.sharding import voice_shard
+    v_lo, v_hi = voice_shard(sh["B"], world, rank)      # contiguous voice range of this rank, no data-path collective
+    Bl = v_hi - v_lo
     T, N, K, NB, sr, hop = sh["T"], sh["N"], sh["K"], sh["NB"], sh["sr"], sh["hop"]
     conf = d.Config(sample_rate=sr, hop_length=hop, n_harmonics=K, n_noise_filters=NB)
 
     # ---- synthetic inputs, generated on the host, this rank's voices only ------------
-    f0h, ch, ah, Hh = O.synthetic_controls(Bl, T, K, NB, sr, hop, seed=1234 + 4, voice_offset=rank * Bl)
+    f0h, ch, ah, Hh = O.synthetic_controls(Bl, T, K, NB, sr, hop, seed=1234 + 4, voice_offset=v_lo)
     gh = torch.randn(Bl, N, generator=torch.Generator().manual_seed(99 + rank))
     host = [t.pin_memory() for t in (f0h, ch, ah, Hh, gh)]
     f0, c, a, H, g = (t.to(dev) for t in host)
@@ -233,7 +234,7 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    seed, voff = 7, rank * Bl
+    seed, voff = 7, v_lo
     counter = [0]
 
     def step():
