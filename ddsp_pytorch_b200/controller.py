@@ -1,0 +1,86 @@
+"""Controller and Decoder around the synthesis path.
+
+The Controller (decoder.py:41-116) is NOT part of the hand-written hot path: its GEMMs and GRU go through torch
+(cuBLAS / cuDNN).  It is restated here only so that a training step and a real-time step can be driven without the
+reference tree; parameter names and shapes follow the reference exactly, so a Lightning checkpoint of the reference
+(`rt/utils.py:7-24` strips the ``model.`` prefix) loads with ``strict=True`` and vice versa.  Everything downstream
+of the controller -- oscillator bank, filtered noise, reverb -- is this package's CUDA path.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .modules import FilteredNoise, OscillatorBank, Reverb
+
+
+def modified_sigmoid(x: torch.Tensor) -> torch.Tensor:
+    """2 * sigmoid(x)^ln(10) + 1e-7   (decoder.py:110-116)."""
+    return 2.0 * torch.sigmoid(x).pow(2.3026) + 1e-7
+
+
+class MLP(nn.Module):
+    """n_layer x (Linear -> LayerNorm -> LeakyReLU); children are named mlp_layer1.. as in decoder.py:9-38."""
+
+    def __init__(self, n_input: int, n_units: int, n_layer: int):
+        super().__init__()
+        self.n_layer = n_layer
+        width = n_input
+        for i in range(1, n_layer + 1):
+            self.add_module(f"mlp_layer{i}", nn.Sequential(nn.Linear(width, n_units), nn.LayerNorm(n_units), nn.LeakyReLU()))
+            width = n_units
+
+    def forward(self, x):
+        for i in range(1, self.n_layer + 1):
+            x = getattr(self, f"mlp_layer{i}")(x)
+        return x
+
+
+class Controller(nn.Module):
+    def __init__(self, conf):
+        super().__init__()
+        self.config = conf
+        u, layers = conf.decoder_mlp_units, conf.decoder_mlp_layers
+        self.mlp_f0 = MLP(1, u, layers)
+        self.mlp_loudness = MLP(1, u, layers)
+        self.num_mlp = 2
+        self.gru = nn.GRU(input_size=2 * u, hidden_size=conf.decoder_gru_units, num_layers=conf.decoder_gru_layers,
+                          batch_first=True)
+        self.mlp_gru = MLP(conf.decoder_gru_units + 2 * u, u, layers)
+        self.dense_harmonic = nn.Linear(u, conf.n_harmonics)
+        self.dense_loudness = nn.Linear(u, 1)
+        self.dense_filter = nn.Linear(u, conf.n_noise_filters)
+
+    def forward(self, batch, hidden=None):
+        lf0 = self.mlp_f0(batch["normalized_cents"])
+        lld = self.mlp_loudness(batch["loudness"])
+        x = torch.cat((lf0, lld), dim=-1)
+        x, h = self.gru(x) if hidden is None else self.gru(x, hidden)
+        x = self.mlp_gru(torch.cat((x, lf0, lld), dim=-1))
+        controls = dict(f0=batch["f0"], c=modified_sigmoid(self.dense_harmonic(x)), hidden=h,
+                        H=modified_sigmoid(self.dense_filter(x)), a=modified_sigmoid(self.dense_loudness(x)))
+        if hidden is not None:
+            return controls, hidden                     # the reference returns the INPUT hidden state here (decoder.py:106-107)
+        return controls
+
+
+class Decoder(nn.Module):
+    """decoder.py:119-147 with the synthesis modules of this package."""
+
+    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None):
+        """`synth`: optional (harmonics, noise, reverb) module triple replacing this package's CUDA modules --
+        used by the CPU-only multi-process tests to drive the trainer with the oracle; never by the product path."""
+        super().__init__()
+        self.controller = Controller(conf)
+        if synth is None:
+            synth = (OscillatorBank(conf), FilteredNoise(conf, seed=noise_seed, voice_offset=voice_offset), Reverb(conf))
+        self.harmonics, self.noise, self.reverb = synth
+
+    def forward(self, z):
+        ctrl = self.controller(z)
+        return self.reverb(self.harmonics(ctrl) + self.noise(ctrl))
+
+    def forward_live(self, z, hidden):
+        ctrl, hidden = self.controller(z, hidden)
+        audio = self.reverb.live_forward(self.harmonics.live(ctrl) + self.noise(ctrl))
+        return audio.cpu().squeeze(0).numpy(), hidden

@@ -1,0 +1,154 @@
+"""The training driver's host logic on CPU: 2-rank gloo gradient averaging == single-process full batch, Lightning-layout
+checkpoints, state-dict parity with the reference Decoder.  The synthesis modules are replaced by oracle-backed
+stand-ins through the Decoder's `synth` test hook (the CUDA modules need a GPU; GPU runs are in test_gpu_train.py)."""
+import os
+import socket
+import sys
+from types import SimpleNamespace
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+import torch.nn as nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference"
+
+
+def small_conf():
+    return SimpleNamespace(sample_rate=4000, hop_length=64, n_harmonics=6, n_noise_filters=9, example_duration=1,
+                           decoder_mlp_units=8, decoder_mlp_layers=2, decoder_gru_units=8, decoder_gru_layers=1)
+
+
+class _Osc(nn.Module):
+    def __init__(self, conf):
+        super().__init__()
+        self.c = conf
+
+    def forward(self, x):
+        from oracle import ddsp_oracle as O
+        return O.oscillator_bank(x["f0"], x["c"], x["a"], self.c.n_harmonics, self.c.sample_rate, self.c.hop_length)
+
+
+class _Noise(nn.Module):
+    def __init__(self, conf, voice_offset):
+        super().__init__()
+        self.c, self.voice_offset, self.calls = conf, voice_offset, 0
+
+    def forward(self, x):
+        from oracle import ddsp_oracle as O
+        from oracle.philox import noise_uniform
+        B, T, _ = x["H"].shape
+        u = torch.from_numpy(noise_uniform(B, T, self.c.hop_length, 3, self.calls, self.voice_offset))
+        self.calls += 1
+        return O.filtered_noise(x["H"], self.c.hop_length, u)
+
+
+class _Reverb(nn.Module):
+    def __init__(self, conf):
+        super().__init__()
+        g = torch.Generator().manual_seed(0)
+        self.sr = conf.sample_rate
+        self.noise = nn.Parameter(torch.rand(conf.sample_rate, generator=g) * 2 - 1)
+        self.decay = nn.Parameter(torch.tensor(5.0))
+        self.wet = nn.Parameter(torch.tensor(0.0))
+
+    def forward(self, x):
+        from oracle import ddsp_oracle as O
+        return O.reverb_apply(x, O.reverb_ir(self.noise, self.decay, self.wet, self.sr))
+
+
+class _Loss(nn.Module):
+    def forward(self, x_pred, x_true):
+        from oracle import ddsp_oracle as O
+        return O.mss_loss(x_pred, x_true["audio"], [64, 128])
+
+
+def _make(conf, voice_offset):
+    from ddsp_pytorch_b200.train import Trainer
+    torch.manual_seed(0)
+    return Trainer(conf, "cpu", synth=(_Osc(conf), _Noise(conf, voice_offset), _Reverb(conf)), loss=_Loss())
+
+
+def _grads_after_step(tr, batch):
+    tr.opt.zero_grad(set_to_none=True)
+    tr.zak.training_loss(batch).backward()
+    from ddsp_pytorch_b200.train import allreduce_mean_
+    n = allreduce_mean_(list(tr.zak.parameters()), bucket_bytes=1024)
+    return {k: p.grad.clone() for k, p in tr.zak.named_parameters() if p.grad is not None}, n
+
+
+def _worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ddsp_pytorch_b200.sharding import voice_shard
+        from ddsp_pytorch_b200.train import synthetic_batch
+        conf = small_conf()
+        lo, hi = voice_shard(4, world, rank)
+        tr = _make(conf, lo)
+        g, n = _grads_after_step(tr, synthetic_batch(conf, hi - lo, "cpu", seed=1, voice_offset=lo))
+        loss = tr.training_step(synthetic_batch(conf, hi - lo, "cpu", seed=1, voice_offset=lo))
+        if rank == 0:
+            ret["grads"] = {k: v.numpy() for k, v in g.items()}
+            ret["collectives"] = n
+            ret["loss"] = float(loss)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gradient_average_equals_full_batch():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ret = mp.Manager().dict()
+    mp.spawn(_worker, args=(2, port, ret), nprocs=2, join=True)
+    from ddsp_pytorch_b200.train import synthetic_batch
+    conf = small_conf()
+    tr = _make(conf, 0)
+    want, n0 = _grads_after_step(tr, synthetic_batch(conf, 4, "cpu", seed=1))
+    assert n0 == 0 and ret["collectives"] > 1              # several buckets at bucket_bytes=1024
+    assert set(want) == set(ret["grads"])
+    for k, v in want.items():
+        got = torch.from_numpy(ret["grads"][k])
+        assert float((got - v).abs().max()) <= 1e-4 * float(v.abs().max()) + 1e-12, k   # fp32 summation order differs
+
+
+def test_checkpoint_layout_and_resume(tmp_path):
+    from ddsp_pytorch_b200.train import synthetic_batch
+    conf = small_conf()
+    tr = _make(conf, 0)
+    batch = synthetic_batch(conf, 2, "cpu", seed=2)
+    l0 = float(tr.training_step(batch))
+    path = str(tmp_path / "lightning_logs" / "version_0" / "checkpoints" / "epoch=0-step=1.ckpt")
+    tr.save_checkpoint(path)
+    ck = torch.load(path)
+    assert all(k.startswith(("model.", "loss.")) for k in ck["state_dict"])           # rt/utils.py:17-22 strips 'model.'
+    stripped = {k[6:]: v for k, v in ck["state_dict"].items() if k.startswith("model")}
+    tr.zak.model.load_state_dict(stripped, strict=True)
+    tr2 = _make(conf, 0)
+    tr2.load_checkpoint(path)
+    tr.zak.model.noise.calls = tr2.zak.model.noise.calls = 1
+    assert tr2.steps == 1
+    assert float(tr2.training_step(batch)) == float(tr.training_step(batch)) and l0 > 0
+    tr.end_epoch(l0)
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference checkout only exists in the build container")
+def test_zak_state_dict_matches_reference_decoder():
+    import subprocess
+    code = r'''
+import torch
+from model.autoencoder.decoder import Decoder
+from config.default import Config
+import ddsp_pytorch_b200 as d
+from ddsp_pytorch_b200.train import Zak
+ref = {"model." + k: (tuple(v.shape), str(v.dtype)) for k, v in Decoder(Config()).state_dict().items()}
+mine = {k: (tuple(v.shape), str(v.dtype)) for k, v in Zak(d.SHIPPED).state_dict().items() if k.startswith("model.")}
+assert ref == mine, set(ref.items()) ^ set(mine.items())
+print("ok")
+'''
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([ROOT, REF]))
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
