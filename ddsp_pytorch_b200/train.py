@@ -80,9 +80,9 @@ class Trainer:
         with torch.autocast("cuda", dtype=torch.float16, enabled=self.amp):
             loss = self.zak.training_loss(batch)
         self.scaler.scale(loss).backward()
+        allreduce_mean_(list(self.zak.parameters()))    # before unscale_: every rank then sees the same inf/nan verdict
         if self.amp:
             self.scaler.unscale_(self.opt)
-        allreduce_mean_(list(self.zak.parameters()))
         self.scaler.step(self.opt)
         self.scaler.update()
         self.steps += 1
