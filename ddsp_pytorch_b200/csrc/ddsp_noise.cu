@@ -369,10 +369,14 @@ __device__ __forceinline__ void team_build_r(const float* H, float* rr, int NB, 
         }                                                                                                       \
     }
 
+// NBc / HOPc > 0: compile-time band count / hop of the common configurations (loops unroll, address arithmetic folds);
+// 0: taken from the run-time arguments.
+template <int NBc, int HOPc>
 __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float* __restrict__ H, const float* __restrict__ noise,
                                                                     float* __restrict__ y, int accumulate, uint2 key,
-                                                                    uint32_t offset, uint32_t voice_offset, int T, int NB, int hop,
-                                                                    long long frames) {
+                                                                    uint32_t offset, uint32_t voice_offset, int T, int NB_rt,
+                                                                    int hop_rt, long long frames) {
+    const int NB = NBc > 0 ? NBc : NB_rt, hop = HOPc > 0 ? HOPc : hop_rt;
     extern __shared__ __align__(16) float smem[];
     const int TS = hop >> 4, FPB = TEAM_BLOCK / TS;
     const int team = threadIdx.x / TS, l = threadIdx.x % TS;
@@ -530,9 +534,12 @@ __host__ __device__ inline TeamBwdLayout team_bwd_layout(int NB, int hop) {
         }                                                                                                       \
     }
 
+template <int NBc, int HOPc>
 __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float* __restrict__ g, const float* __restrict__ noise,
                                                                     float* __restrict__ gH, uint2 key, uint32_t offset,
-                                                                    uint32_t voice_offset, int T, int NB, int hop, long long frames) {
+                                                                    uint32_t voice_offset, int T, int NB_rt, int hop_rt,
+                                                                    long long frames) {
+    const int NB = NBc > 0 ? NBc : NB_rt, hop = HOPc > 0 ? HOPc : hop_rt;
     extern __shared__ __align__(16) float smem[];
     const int TS = hop >> 4, FPB = TEAM_BLOCK / TS;
     const int team = threadIdx.x / TS, l = threadIdx.x % TS;
@@ -708,10 +715,19 @@ extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, 
         const int FPB = TEAM_BLOCK / (hop / 16);
         const size_t tsm = sizeof(float) * (size_t)team_layout(NB, hop).total * FPB;
         if (tsm <= 200 * 1024) {
-            if (reserve_smem(noise_fwd_team_kernel, tsm, "noise_fwd_team_kernel")) return 1;
             const long long frames = (long long)B * T;
-            noise_fwd_team_kernel<<<(unsigned)((frames + FPB - 1) / FPB), TEAM_BLOCK, tsm, static_cast<cudaStream_t>(stream)>>>(
-                H, noise, y, accumulate, key, offset, voice_offset, T, NB, hop, frames);
+            const unsigned grid = (unsigned)((frames + FPB - 1) / FPB);
+            cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define NOISE_FWD(NBc, HOPc)                                                                                         \
+    do {                                                                                                             \
+        if (reserve_smem(noise_fwd_team_kernel<NBc, HOPc>, tsm, "noise_fwd_team_kernel")) return 1;                  \
+        noise_fwd_team_kernel<NBc, HOPc><<<grid, TEAM_BLOCK, tsm, st>>>(H, noise, y, accumulate, key, offset,        \
+                                                                        voice_offset, T, NB, hop, frames);           \
+    } while (0)
+            if (NB == 65 && hop == 512) NOISE_FWD(65, 512);
+            else if (NB == 195 && hop == 512) NOISE_FWD(195, 512);
+            else NOISE_FWD(0, 0);
+#undef NOISE_FWD
             DDSP_CHECK_LAUNCH("noise_fwd_team_kernel");
             return 0;
         }
@@ -733,10 +749,19 @@ extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH
         const int FPB = TEAM_BLOCK / (hop / 16);
         const size_t tsm = sizeof(float) * (size_t)team_bwd_layout(NB, hop).total * FPB;
         if (tsm <= 200 * 1024) {
-            if (reserve_smem(noise_bwd_team_kernel, tsm, "noise_bwd_team_kernel")) return 1;
             const long long frames = (long long)B * T;
-            noise_bwd_team_kernel<<<(unsigned)((frames + FPB - 1) / FPB), TEAM_BLOCK, tsm, static_cast<cudaStream_t>(stream)>>>(
-                g, noise, gH, key, offset, voice_offset, T, NB, hop, frames);
+            const unsigned grid = (unsigned)((frames + FPB - 1) / FPB);
+            cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define NOISE_BWD(NBc, HOPc)                                                                                         \
+    do {                                                                                                             \
+        if (reserve_smem(noise_bwd_team_kernel<NBc, HOPc>, tsm, "noise_bwd_team_kernel")) return 1;                  \
+        noise_bwd_team_kernel<NBc, HOPc><<<grid, TEAM_BLOCK, tsm, st>>>(g, noise, gH, key, offset, voice_offset, T,  \
+                                                                        NB, hop, frames);                            \
+    } while (0)
+            if (NB == 65 && hop == 512) NOISE_BWD(65, 512);
+            else if (NB == 195 && hop == 512) NOISE_BWD(195, 512);
+            else NOISE_BWD(0, 0);
+#undef NOISE_BWD
             DDSP_CHECK_LAUNCH("noise_bwd_team_kernel");
             return 0;
         }
