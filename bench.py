@@ -44,6 +44,7 @@ def parse_args():
     p.add_argument("--cpu-voices", type=int, default=2, help="voices in the bounded CPU sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     p.add_argument("--e2e-chunk", type=int, default=64, help="voices per chunk of the host pipeline")
     return p.parse_args()
 
@@ -59,7 +60,8 @@ def workload_config(args, sh, extra=None):
            "voices": sh["B"], "frames": sh["T"], "samples_per_voice": sh["N"], "harmonics": sh["K"],
            "noise_bands": sh["NB"], "sample_rate": sh["sr"], "hop": sh["hop"],
            "cache": "per-step working set (c 0.39 GB + g/y/z 0.79 GB each at 1 GPU) exceeds the 126 MB L2; no explicit flush",
-           "parallelism": f"voices sharded over {args.gpus} rank(s), no collective"}
+           "parallelism": f"voices sharded over {args.gpus} rank(s), no collective",
+           "launch": "eager" if args.no_graph else "CUDA graph replay of the step"}
     if extra:
         cfg.update(extra)
     return cfg
@@ -235,16 +237,36 @@ def run_b200(args):
         return float(t.item())
 
     seed, voff = 7, v_lo
-    counter = [0]
+    calls = torch.zeros(1, dtype=torch.int32, device=dev)      # device-side call counter: fresh Philox offset per step
 
-    def step():
+    def step_body():
         """resident inputs -> y = noise(H); y += osc(f0,c,a); backward from g.  6 launches of this repo's kernels."""
-        c.grad = a.grad = H.grad = None
-        y = ops.filtered_noise(H, hop, seed=seed, offset=counter[0], voice_offset=voff)
+        calls.add_(1)
+        y = ops.filtered_noise(H, hop, seed=seed, offset=0, voice_offset=voff, offset_tensor=calls)
         y = ops.oscillator_bank(f0, c, a, sr, hop, out=y)
         y.backward(g)
-        counter[0] += 1
         return y
+
+    def eager_step():
+        c.grad = a.grad = H.grad = None
+        return step_body()
+
+    step = eager_step
+    if not args.no_graph:
+        # the step is launch-bound once the voices are spread over 8 GPUs (1.3 ms of kernels): capture it once and
+        # replay it; the gradients land in the same buffers on every replay, the noise counter advances on the device
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                eager_step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        c.grad = a.grad = H.grad = None
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            step_body()
+        step = graph.replay
 
     sampler = ClockSampler(local) if rank == 0 else None
     t_load0 = time.time()
@@ -303,8 +325,8 @@ def run_b200(args):
         "osc_synth_kernel": lambda: _lib.call("ddsp_osc_synthesize", P(f0), P(ad_), P(state), P(y), P(z), 0, Bl, T, K, hop, sr, st),
         "osc_grad_kernel": lambda: _lib.call("ddsp_osc_grad_segments", P(g), P(f0), P(ad_), P(z), P(state), P(scratch), Bl, T, K, hop, sr, st),
         "osc_finalize_kernel": lambda: _lib.call("ddsp_osc_grad_finalize", P(f0), P(state), P(scratch), P(gc), P(ga), Bl, T, K, hop, sr, st),
-        "noise_fwd_kernel": lambda: _lib.call("ddsp_noise_forward", P(Hd_), None, P(y), 0, seed, 0, voff, Bl, T, NB, hop, st),
-        "noise_bwd_kernel": lambda: _lib.call("ddsp_noise_backward", P(g), None, P(gH), seed, 0, voff, Bl, T, NB, hop, st),
+        "noise_fwd_kernel": lambda: _lib.call("ddsp_noise_forward", P(Hd_), None, P(y), 0, seed, 0, None, voff, Bl, T, NB, hop, st),
+        "noise_bwd_kernel": lambda: _lib.call("ddsp_noise_backward", P(g), None, P(gH), seed, 0, None, voff, Bl, T, NB, hop, st),
     }
     kernels_ms = {name: time_call(fn) for name, fn in calls.items()}
     fp32_peak = ops.probe_fp32_fma_tflops()

@@ -110,8 +110,10 @@ __device__ __forceinline__ void load_noise(const NoiseSmem& s, const float* __re
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512) noise_fwd_kernel(const float* __restrict__ H, const float* __restrict__ noise,
                                                         float* __restrict__ y, int accumulate, uint2 key, uint32_t offset,
-                                                        uint32_t voice_offset, int T, int NB, int hop) {
+                                                        const uint32_t* __restrict__ offset_dev, uint32_t voice_offset, int T,
+                                                        int NB, int hop) {
     extern __shared__ __align__(16) float smem[];
+    if (offset_dev) offset += *offset_dev;
     const NoiseSmem s = carve_noise_smem(smem, NB, hop);
     const int t = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const size_t frame = (size_t)b * T + t;
@@ -192,8 +194,10 @@ __host__ __device__ inline size_t noise_bwd_smem_floats(int NB, int hop) {
 
 __global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict__ g, const float* __restrict__ noise,
                                                         float* __restrict__ gH, uint2 key, uint32_t offset,
-                                                        uint32_t voice_offset, int T, int NB, int hop, int nsl) {
+                                                        const uint32_t* __restrict__ offset_dev, uint32_t voice_offset, int T,
+                                                        int NB, int hop, int nsl) {
     extern __shared__ __align__(16) float smem[];
+    if (offset_dev) offset += *offset_dev;
     const int M = 2 * (NB - 1), half = NB - 1, TP = noise_tp(NB), PADL = TP + 8;
     float* ct = smem;
     float* dr = ct + ((M + 3) & ~3);
@@ -374,9 +378,11 @@ __device__ __forceinline__ void team_build_r(const float* H, float* rr, int NB, 
 template <int NBc, int HOPc>
 __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float* __restrict__ H, const float* __restrict__ noise,
                                                                     float* __restrict__ y, int accumulate, uint2 key,
-                                                                    uint32_t offset, uint32_t voice_offset, int T, int NB_rt,
-                                                                    int hop_rt, long long frames) {
+                                                                    uint32_t offset, const uint32_t* __restrict__ offset_dev,
+                                                                    uint32_t voice_offset, int T, int NB_rt, int hop_rt,
+                                                                    long long frames) {
     const int NB = NBc > 0 ? NBc : NB_rt, hop = HOPc > 0 ? HOPc : hop_rt;
+    if (offset_dev) offset += *offset_dev;
     extern __shared__ __align__(16) float smem[];
     const int TS = hop >> 4, FPB = TEAM_BLOCK / TS;
     const int team = threadIdx.x / TS, l = threadIdx.x % TS;
@@ -537,9 +543,10 @@ __host__ __device__ inline TeamBwdLayout team_bwd_layout(int NB, int hop) {
 template <int NBc, int HOPc>
 __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float* __restrict__ g, const float* __restrict__ noise,
                                                                     float* __restrict__ gH, uint2 key, uint32_t offset,
-                                                                    uint32_t voice_offset, int T, int NB_rt, int hop_rt,
-                                                                    long long frames) {
+                                                                    const uint32_t* __restrict__ offset_dev, uint32_t voice_offset,
+                                                                    int T, int NB_rt, int hop_rt, long long frames) {
     const int NB = NBc > 0 ? NBc : NB_rt, hop = HOPc > 0 ? HOPc : hop_rt;
+    if (offset_dev) offset += *offset_dev;
     extern __shared__ __align__(16) float smem[];
     const int TS = hop >> 4, FPB = TEAM_BLOCK / TS;
     const int team = threadIdx.x / TS, l = threadIdx.x % TS;
@@ -707,7 +714,8 @@ static int reserve_smem(Kern kern, size_t bytes, const char* name) {
 using namespace ddsp;
 
 extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, int accumulate, uint64_t seed,
-                                  uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop, void* stream) {
+                                  uint32_t offset, const uint32_t* offset_dev, uint32_t voice_offset, int B, int T, int NB,
+                                  int hop, void* stream) {
     if (check_noise_shape("ddsp_noise_forward", B, T, NB, hop)) return 1;
     DDSP_REQUIRE(H && y, "ddsp_noise_forward: null pointer argument");
     const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
@@ -722,7 +730,7 @@ extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, 
     do {                                                                                                             \
         if (reserve_smem(noise_fwd_team_kernel<NBc, HOPc>, tsm, "noise_fwd_team_kernel")) return 1;                  \
         noise_fwd_team_kernel<NBc, HOPc><<<grid, TEAM_BLOCK, tsm, st>>>(H, noise, y, accumulate, key, offset,        \
-                                                                        voice_offset, T, NB, hop, frames);           \
+                                                                        offset_dev, voice_offset, T, NB, hop, frames);           \
     } while (0)
             if (NB == 65 && hop == 512) NOISE_FWD(65, 512);
             else if (NB == 195 && hop == 512) NOISE_FWD(195, 512);
@@ -735,13 +743,14 @@ extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, 
     const size_t smem = sizeof(float) * noise_smem_floats(NB, hop);
     if (reserve_smem(noise_fwd_kernel, smem, "noise_fwd_kernel")) return 1;
     noise_fwd_kernel<<<dim3(T, B), hop / 8, smem, static_cast<cudaStream_t>(stream)>>>(H, noise, y, accumulate, key, offset,
-                                                                                      voice_offset, T, NB, hop);
+                                                                                      offset_dev, voice_offset, T, NB, hop);
     DDSP_CHECK_LAUNCH("noise_fwd_kernel");
     return 0;
 }
 
 extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH, uint64_t seed, uint32_t offset,
-                                   uint32_t voice_offset, int B, int T, int NB, int hop, void* stream) {
+                                   const uint32_t* offset_dev, uint32_t voice_offset, int B, int T, int NB, int hop,
+                                   void* stream) {
     if (check_noise_shape("ddsp_noise_backward", B, T, NB, hop)) return 1;
     DDSP_REQUIRE(g && gH, "ddsp_noise_backward: null pointer argument");
     const uint2 key = make_uint2((uint32_t)(seed & 0xffffffffu), (uint32_t)(seed >> 32));
@@ -755,7 +764,7 @@ extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH
 #define NOISE_BWD(NBc, HOPc)                                                                                         \
     do {                                                                                                             \
         if (reserve_smem(noise_bwd_team_kernel<NBc, HOPc>, tsm, "noise_bwd_team_kernel")) return 1;                  \
-        noise_bwd_team_kernel<NBc, HOPc><<<grid, TEAM_BLOCK, tsm, st>>>(g, noise, gH, key, offset, voice_offset, T,  \
+        noise_bwd_team_kernel<NBc, HOPc><<<grid, TEAM_BLOCK, tsm, st>>>(g, noise, gH, key, offset, offset_dev, voice_offset, T,  \
                                                                         NB, hop, frames);                            \
     } while (0)
             if (NB == 65 && hop == 512) NOISE_BWD(65, 512);
@@ -771,8 +780,8 @@ extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH
     DDSP_REQUIRE(threads <= 512, "ddsp_noise_backward: NB=%d needs %d threads per frame (max 512)", NB, threads);
     const size_t smem = sizeof(float) * noise_bwd_smem_floats(NB, hop);
     if (reserve_smem(noise_bwd_kernel, smem, "noise_bwd_kernel")) return 1;
-    noise_bwd_kernel<<<dim3(T, B), threads, smem, static_cast<cudaStream_t>(stream)>>>(g, noise, gH, key, offset, voice_offset,
-                                                                                      T, NB, hop, nsl);
+    noise_bwd_kernel<<<dim3(T, B), threads, smem, static_cast<cudaStream_t>(stream)>>>(g, noise, gH, key, offset, offset_dev,
+                                                                                      voice_offset, T, NB, hop, nsl);
     DDSP_CHECK_LAUNCH("noise_bwd_kernel");
     return 0;
 }

@@ -79,7 +79,7 @@ def oscillator_bank(f0: torch.Tensor, c: torch.Tensor, a: torch.Tensor, sample_r
 class _FilteredNoise(torch.autograd.Function):
     @staticmethod
     def forward(ctx, H, hop: int, seed: int, offset: int, voice_offset: int, noise: Optional[torch.Tensor],
-                out: Optional[torch.Tensor]):
+                out: Optional[torch.Tensor], offset_tensor: Optional[torch.Tensor]):
         H_ = _f32(H)
         B, T, NB = H_.shape
         dev = H_.device
@@ -92,9 +92,11 @@ class _FilteredNoise(torch.autograd.Function):
             accumulate = out is not None
             y = out if accumulate else torch.empty(B, T * hop, dtype=torch.float32, device=dev)
             _lib.call("ddsp_noise_forward", H_.data_ptr(), noise_.data_ptr() if noise_ is not None else None, y.data_ptr(),
-                      int(accumulate), seed, offset, voice_offset, B, T, NB, hop, _stream())
+                      int(accumulate), seed, offset, offset_tensor.data_ptr() if offset_tensor is not None else None,
+                      voice_offset, B, T, NB, hop, _stream())
         ctx.args = (B, T, NB, hop, seed, offset, voice_offset, H.shape, H.dtype)
         ctx.noise = noise_
+        ctx.offset_tensor = offset_tensor
         if accumulate:
             ctx.mark_dirty(out)
         return y
@@ -107,17 +109,22 @@ class _FilteredNoise(torch.autograd.Function):
         with torch.cuda.device(dev):
             gH = torch.empty(B, T, NB, dtype=torch.float32, device=dev)
             _lib.call("ddsp_noise_backward", g_.data_ptr(), ctx.noise.data_ptr() if ctx.noise is not None else None,
-                      gH.data_ptr(), seed, offset, voice_offset, B, T, NB, hop, _stream())
+                      gH.data_ptr(), seed, offset, ctx.offset_tensor.data_ptr() if ctx.offset_tensor is not None else None,
+                      voice_offset, B, T, NB, hop, _stream())
         g_out = g if ctx.needs_input_grad[6] else None
-        return gH.view(H_shape).to(H_dtype), None, None, None, None, None, g_out
+        return gH.view(H_shape).to(H_dtype), None, None, None, None, None, g_out, None
 
 
 def filtered_noise(H: torch.Tensor, hop: int, seed: int = 0, offset: int = 0, voice_offset: int = 0,
-                   noise: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                   noise: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                   offset_tensor: Optional[torch.Tensor] = None) -> torch.Tensor:
     """H [B,T,NB] -> [B,T*hop]  (FilteredNoise.forward, filtered_noise.py:40-53).  ``noise`` [B,T,hop] in [-1,1)
-    replaces the in-kernel Philox stream (parity tests inject the reference's draw this way)."""
+    replaces the in-kernel Philox stream (parity tests inject the reference's draw this way).  ``offset_tensor``:
+    a one-element int32 CUDA tensor added to ``offset`` on the device (a call counter a CUDA graph can advance)."""
+    if offset_tensor is not None and not (offset_tensor.is_cuda and offset_tensor.dtype == torch.int32 and offset_tensor.numel() == 1):
+        raise RuntimeError("filtered_noise: offset_tensor must be a one-element int32 CUDA tensor")
     return _FilteredNoise.apply(H, int(hop), int(seed) & (2 ** 64 - 1), int(offset) & 0xFFFFFFFF,
-                                int(voice_offset) & 0xFFFFFFFF, noise, out)
+                                int(voice_offset) & 0xFFFFFFFF, noise, out, offset_tensor)
 
 
 def noise_uniform(B: int, T: int, hop: int, seed: int, offset: int = 0, voice_offset: int = 0, device="cuda") -> torch.Tensor:

@@ -86,15 +86,17 @@ int ddsp_osc_live(const float* f0, const float* c, const float* a, const float* 
 /* y[B,N] (+)= per-frame causal convolution of uniform noise with the windowed zero-phase FIR of H.
  *   H [B,T,NB].  noise [B,T,hop] in [-1,1) or NULL: NULL draws the noise in-kernel with
  *   Philox4x32-10, key = seed, counter = (j>>2, t, voice_offset + b, offset), word j&3,
- *   u = (word>>8)*2^-24, noise = 2u-1  (oracle/philox.py is the CPU statement of this layout). */
+ *   u = (word>>8)*2^-24, noise = 2u-1  (oracle/philox.py is the CPU statement of this layout).
+ *   offset_dev: NULL, or a DEVICE uint32 added to `offset` when the kernel runs -- a call counter that lives
+ *   on the device lets a captured CUDA graph draw fresh noise on every replay. */
 int ddsp_noise_forward(const float* H, const float* noise, float* y, int accumulate, uint64_t seed,
-                       uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop,
-                       void* stream);
+                       uint32_t offset, const uint32_t* offset_dev, uint32_t voice_offset, int B, int T,
+                       int NB, int hop, void* stream);
 
 /* gH [B,T,NB] = d sum(g*y) / dH with the same noise (regenerated from the same seed/offset). */
 int ddsp_noise_backward(const float* g, const float* noise, float* gH, uint64_t seed,
-                        uint32_t offset, uint32_t voice_offset, int B, int T, int NB, int hop,
-                        void* stream);
+                        uint32_t offset, const uint32_t* offset_dev, uint32_t voice_offset, int B, int T,
+                        int NB, int hop, void* stream);
 
 /* The noise block itself [B,T,hop] (for tests of the Philox layout and for injecting it elsewhere). */
 int ddsp_noise_uniform(float* out, uint64_t seed, uint32_t offset, uint32_t voice_offset, int B,

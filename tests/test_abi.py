@@ -60,7 +60,7 @@ def test_size_queries_and_argument_validation_need_no_gpu(lib_path):
     with pytest.raises(RuntimeError, match="null"):
         _lib.call("ddsp_osc_forward", None, None, None, None, None, None, 0, 1, 3, 4, 8, 16000, None)
     with pytest.raises(RuntimeError, match="FIR length"):
-        _lib.call("ddsp_noise_forward", 1, None, 1, 0, 0, 0, 0, 1, 2, 65, 64, None)
+        _lib.call("ddsp_noise_forward", 1, None, 1, 0, 0, 0, None, 0, 1, 2, 65, 64, None)
 
 
 def test_ops_refuse_cpu_tensors():
