@@ -192,7 +192,7 @@ struct MssFast {
 };
 
 template <int N>
-__global__ void __launch_bounds__(MssFast<N>::THREADS) mss_fast_kernel(const float* __restrict__ xp, const float* __restrict__ xt,
+__global__ void __launch_bounds__(MssFast<N>::THREADS, 512 / MssFast<N>::THREADS) mss_fast_kernel(const float* __restrict__ xp, const float* __restrict__ xt,
                                                                       double* __restrict__ loss, double* __restrict__ terms,
                                                                       float* __restrict__ gx, const float* __restrict__ window,
                                                                       int Nsig, int hop, int F, double inv_count, double alpha_d,
