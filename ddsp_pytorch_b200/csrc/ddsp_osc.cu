@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_grad_kernel(
     __shared__ float red[2][16];
     constexpr int R = 2 * RP;
     const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, NT = blockDim.x;
-    const int stride = 2 * NT + 4;
+    const int stride = ((2 * NT + 3) & ~3) + 4;          // multiple of 4 floats: the float4 row sweeps stay 16-byte aligned
     const SegGeom g = seg_geom(s, T, hop);
     const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
     const int kmax = max(kact[fL], kact[fR]);
@@ -577,7 +577,7 @@ template <int RP>
 static int launch_grad(const float* g, const float* a, const float* z, const OscState& S, float2* gseg, float2* gaseg, int B,
                        int T, int K, int hop, cudaStream_t st) {
     const int NT = hop / (2 * RP);
-    const size_t smem = sizeof(float) * GRAD_CH * (2 * NT + 4);
+    const size_t smem = sizeof(float) * GRAD_CH * (((2 * NT + 3) & ~3) + 4);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(osc_grad_kernel<RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         DDSP_REQUIRE(e == cudaSuccess, "osc_grad_kernel: cannot reserve %zu B of shared memory: %s", smem,

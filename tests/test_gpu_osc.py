@@ -41,7 +41,12 @@ def test_golden_waveform_and_grads(golden, name):
 
 
 @pytest.mark.parametrize("B,T,K,sr,hop", [(3, 20, 100, 16000, 512), (2, 9, 180, 44100, 512), (2, 7, 256, 48000, 512),
-                                          (1, 5, 60, 44100, 64), (2, 6, 33, 22050, 128), (1, 4, 7, 8000, 24)])
+                                          (1, 5, 60, 44100, 64), (2, 6, 33, 22050, 128), (1, 4, 7, 8000, 24),
+                                          # ragged shapes: hops that are not a multiple of 4 (per-sample masked pair path),
+                                          # a single frame, a single harmonic, the largest hops (16 samples per thread)
+                                          (2, 3, 5, 8000, 2), (1, 4, 9, 8000, 6), (2, 5, 12, 16000, 10), (1, 1, 2, 16000, 512),
+                                          (3, 1, 40, 48000, 16), (1, 3, 64, 48000, 1024), (1, 2, 30, 48000, 2048),
+                                          (1, 2, 17, 44100, 4096)])
 def test_against_oracle(B, T, K, sr, hop):
     from oracle import ddsp_oracle as O
     f0, c, a, _ = O.synthetic_controls(B, T, K, 5, sr, hop, seed=100 + K)

@@ -90,6 +90,7 @@ def test_mss_golden(golden):
 
 
 @pytest.mark.parametrize("B,N,n_ffts", [(3, 5000, [64, 128, 256]), (1, 2050, [4096, 2048]), (2, 777, [16, 32, 8]),
+                                        (1, 1001, [4, 8, 512, 1024]), (5, 333, [128]),
                                         (4, 64000, [2048, 1024, 512, 256, 128, 64])])
 def test_mss_against_oracle(B, N, n_ffts):
     from ddsp_pytorch_b200 import ops
