@@ -1,0 +1,44 @@
+"""Streaming blocks through RealtimeSynth == the same decoder run block by block against the fp64 oracle's live path."""
+import os
+import sys
+
+import pytest
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def test_blocks_match_oracle_live_path_and_keep_state():
+    import test_train_gloo as H
+    from ddsp_pytorch_b200.realtime import RealtimeSynth
+    from ddsp_pytorch_b200.train import synthetic_batch
+    from oracle import ddsp_oracle as O
+    from oracle.philox import noise_uniform
+    conf = H.small_conf()
+    conf.sample_rate, conf.hop_length, conf.n_noise_filters = 4000, 64, 9
+    torch.manual_seed(1)
+    rt = RealtimeSynth(conf, "cuda:0", frames_per_block=4, noise_seed=3)
+    rt.decoder.reverb.wet.data.fill_(1.0)                       # make the reverb tail audible
+    dec = rt.decoder
+    # oracle-side state
+    last = torch.zeros(conf.n_harmonics, dtype=torch.float64)
+    buf = torch.zeros(1, conf.sample_rate, dtype=torch.float64)
+    ir = O.reverb_ir(dec.reverb.noise.detach().cpu().double(), dec.reverb.decay.detach().cpu().double(),
+                     dec.reverb.wet.detach().cpu().double(), conf.sample_rate)
+    for blk in range(5):
+        feats = synthetic_batch(conf, 1, "cpu", seed=10 + blk)
+        z = {k: v[:, :4].contiguous() for k, v in feats.items() if k != "audio"}
+        got = torch.from_numpy(rt.process(z).copy()).double()
+        with torch.no_grad():
+            ctrl, _ = dec.controller({k: v.cuda() for k, v in z.items()}, rt.hidden)
+        c, a, Hh, f0 = (ctrl[k].detach().cpu().double() for k in ("c", "a", "H", "f0"))
+        harm, last = O.oscillator_bank_live(f0, c, a, last, conf.n_harmonics, conf.sample_rate, conf.hop_length)
+        u = torch.from_numpy(noise_uniform(1, 4, conf.hop_length, 3, blk, 0)).double()
+        dry = harm + O.filtered_noise(Hh, conf.hop_length, u)
+        want, buf = O.reverb_live(buf, dry, ir)
+        err = float((got - want.view(-1)).abs().max())
+        print(f"block {blk}: |cuda - oracle64| = {err:.2e}, max|y| = {float(want.abs().max()):.3f}")
+        assert err <= 1e-4 * max(1.0, float(want.abs().max()))
+    st = rt.stats()
+    assert st["blocks"] == 5 and st["p50_ms"] > 0
