@@ -319,3 +319,18 @@ def oscillator_live(f0, c, a, last_phases, sample_rate: int, hop: int):
         _lib.call("ddsp_osc_live", f0_.data_ptr(), c_.data_ptr(), a_.data_ptr(), last_in.data_ptr(), last_out.data_ptr(),
                   y.data_ptr(), state.data_ptr(), B, T, K, int(hop), int(sample_rate), _stream())
     return y, last_out
+
+
+def loudness(signal: torch.Tensor, a_weight: torch.Tensor, n_fft: int, hop: int) -> torch.Tensor:
+    """signal [B,N] -> loudness [B,F,1]  (LoudnessEncoder.forward, encoder.py:141-156).  No gradient: the encoder runs
+    under no_grad in the reference (encoder.py:51)."""
+    x, aw = _f32(signal), _f32(a_weight)
+    B, N = x.shape
+    if aw.numel() != n_fft // 2 + 1:
+        raise RuntimeError(f"loudness: a_weight has {aw.numel()} entries, n_fft={n_fft} needs {n_fft // 2 + 1}")
+    with torch.cuda.device(x.device):
+        lib = _lib.load()
+        F_ = lib.ddsp_loudness_frames(N, n_fft, hop)
+        out = torch.empty(B, max(F_, 0), 1, dtype=torch.float32, device=x.device)
+        _lib.call("ddsp_loudness_forward", x.data_ptr(), aw.data_ptr(), out.data_ptr(), B, N, n_fft, hop, _stream())
+    return out

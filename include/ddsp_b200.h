@@ -160,6 +160,16 @@ int ddsp_mss_backward(const float* gloss, const float* gx_saved, float* gx_out, 
                       void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Loudness feature  --  LoudnessEncoder.forward, model/autoencoder/encoder.py:141-156
+ *   out[B,F] = mean_k( (20 log10(|STFT(x)[k]| + 1e-20) + a_weight[k]) / 90 + 1 ),  rectangular window,
+ *   center=False, F = ddsp_loudness_frames(N, n_fft, hop) = 1 + (N - n_fft)/hop, a_weight [n_fft/2+1] in dB.
+ *   n_fft a power of two in [8,4096].  Forward only (the encoder runs under no_grad, encoder.py:51).
+ * ------------------------------------------------------------------------------------------ */
+int ddsp_loudness_frames(int N, int n_fft, int hop);
+int ddsp_loudness_forward(const float* x, const float* a_weight, float* out, int B, int N, int n_fft,
+                          int hop, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * The transform underneath the reverb and the spectral loss, on its own: `batch` complex FFTs of
  * size n (power of two in [8,4096]), interleaved (re,im) fp32 (fp64 = 0) or fp64 (fp64 != 0), in
  * natural order; inverse != 0 is the unnormalised inverse.  Replaces the cuFFT calls the reference

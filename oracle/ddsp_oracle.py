@@ -273,3 +273,35 @@ def synthetic_controls(B: int, T: int, K: int, NB: int, sample_rate: int, hop: i
         a[b] = modified_sigmoid(torch.randn(T, 1, generator=g, dtype=torch.float64))
         H[b] = modified_sigmoid(torch.randn(T, NB, generator=g, dtype=torch.float64))
     return f0.to(dtype), c.to(dtype), a.to(dtype), H.to(dtype)
+
+
+# ----------------------------------------------------------------------------------------
+# Loudness encoder  (model/autoencoder/encoder.py:131-156)
+# ----------------------------------------------------------------------------------------
+def a_weighting(freqs, min_db: float = -80.0):
+    """A-weighting in dB at `freqs` [Hz] -- the IEC 61672 curve as librosa.A_weighting states it (the reference calls
+    librosa, encoder.py:138; librosa is not installable here, so this restatement is pinned by the standard's tabulated
+    values only: 0 dB at 1 kHz, -19.1 dB at 100 Hz, +1.2 dB at 2.5 kHz, -2.5 dB at 10 kHz -- tests/test_oracle.py)."""
+    import numpy as np
+    f_sq = np.asarray(freqs, dtype=np.float64) ** 2.0
+    c = np.array([12194.217, 20.598997, 107.65265, 737.86223]) ** 2.0
+    with np.errstate(divide="ignore"):
+        w = 2.0 + 20.0 * (np.log10(c[0]) + 2.0 * np.log10(f_sq) - np.log10(f_sq + c[0]) - np.log10(f_sq + c[1])
+                          - 0.5 * np.log10(f_sq + c[2]) - 0.5 * np.log10(f_sq + c[3]))
+    return np.maximum(min_db, w)
+
+
+def loudness_a_weight(n_fft: int, sample_rate: int) -> torch.Tensor:
+    """The `a_weight` parameter of LoudnessEncoder (encoder.py:137-139): fp32 bin frequencies, weights in fp32."""
+    import numpy as np
+    freqs = np.linspace(0, float(sample_rate) / 2, int(1 + n_fft // 2), endpoint=True, dtype="float32")
+    return torch.from_numpy(a_weighting(freqs).astype("float32"))
+
+
+def loudness_encoder(signal: torch.Tensor, a_weight: torch.Tensor, n_fft: int, hop: int) -> torch.Tensor:
+    """``LoudnessEncoder.forward`` (encoder.py:141-156): rectangular-window STFT, center=False."""
+    stft = torch.stft(signal, n_fft=n_fft, hop_length=hop, center=False, return_complex=True).permute(0, 2, 1)
+    db = torch.log10(torch.abs(stft) + 1e-20) * 20
+    db = db + a_weight.to(db.dtype)
+    db = db / 90 + 1
+    return torch.mean(db, dim=-1, keepdim=True)
