@@ -26,6 +26,7 @@ def main():
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--global-batch", type=int, default=32)
     p.add_argument("--amp", action="store_true", help="fp16 autocast of the Controller (reference: precision=16)")
+    p.add_argument("--graph", action="store_true", help="capture the whole training step as a CUDA graph and replay it")
     args = p.parse_args()
     import ddsp_pytorch_b200 as d
     from ddsp_pytorch_b200.sharding import max_over_ranks, voice_shard
@@ -40,7 +41,7 @@ def main():
     conf = d.SHIPPED
     lo, hi = voice_shard(args.global_batch, world, rank)
     torch.manual_seed(0)
-    tr = Trainer(conf, dev, amp=args.amp, noise_seed=7, voice_offset=lo)
+    tr = Trainer(conf, dev, amp=args.amp, noise_seed=7, voice_offset=lo, graph=args.graph)
     batch = synthetic_batch(conf, hi - lo, dev, seed=2, voice_offset=lo)
     T = batch["f0"].shape[1]
     N = T * conf.hop_length
@@ -111,7 +112,7 @@ def main():
     if rank == 0:
         n_params = sum(p_.numel() for p_ in zak.parameters() if p_.requires_grad)
         print(json.dumps({"workload": f"cfg2 training step: global batch {args.global_batch} x {N} samples @ {conf.sample_rate} Hz, "
-                                      f"K={conf.n_harmonics}, NB={conf.n_noise_filters}, 6-scale MSS, Adam, amp={args.amp}",
+                                      f"K={conf.n_harmonics}, NB={conf.n_noise_filters}, 6-scale MSS, Adam, amp={args.amp}, graph={args.graph}",
                           "n_gpus": world, "ms_per_step": ms, "samples_per_s": args.global_batch * N / (ms * 1e-3),
                           "loss": float(loss), "trainable_params": n_params, "allreduce_bytes": 4 * n_params,
                           "phases_rank0": phases}), flush=True)

@@ -67,13 +67,14 @@ class Controller(nn.Module):
 class Decoder(nn.Module):
     """decoder.py:119-147 with the synthesis modules of this package."""
 
-    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None):
+    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None, device_counter: bool = False):
         """`synth`: optional (harmonics, noise, reverb) module triple replacing this package's CUDA modules --
         used by the CPU-only multi-process tests to drive the trainer with the oracle; never by the product path."""
         super().__init__()
         self.controller = Controller(conf)
         if synth is None:
-            synth = (OscillatorBank(conf), FilteredNoise(conf, seed=noise_seed, voice_offset=voice_offset), Reverb(conf))
+            synth = (OscillatorBank(conf), FilteredNoise(conf, seed=noise_seed, voice_offset=voice_offset,
+                                                         device_counter=device_counter), Reverb(conf))
         self.harmonics, self.noise, self.reverb = synth
 
     def forward(self, z):

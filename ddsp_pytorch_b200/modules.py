@@ -36,14 +36,22 @@ class FilteredNoise(nn.Module):
     global index of this rank's first voice, which makes the draw independent of batch sharding.
     """
 
-    def __init__(self, conf, seed=None, voice_offset: int = 0):
+    def __init__(self, conf, seed=None, voice_offset: int = 0, device_counter: bool = False):
         super().__init__()
         self.block_size = conf.hop_length
         self.seed = int(torch.initial_seed() if seed is None else seed) & (2 ** 63 - 1)
         self.voice_offset = int(voice_offset)
         self.calls = 0
+        # device_counter: keep the call counter on the device and advance it there, so that a CUDA graph that captured
+        # this forward (and its backward) draws fresh noise on every replay.  Valid for forward -> backward alternation.
+        self.device_counter = bool(device_counter)
+        if self.device_counter:
+            self.register_buffer("_calls_dev", torch.zeros(1, dtype=torch.int32), persistent=False)
 
     def forward(self, x, noise=None):
+        if self.device_counter and noise is None:
+            self._calls_dev.add_(1)
+            return ops.filtered_noise(x["H"], self.block_size, self.seed, 0, self.voice_offset, offset_tensor=self._calls_dev)
         offset = self.calls
         self.calls += 1
         return ops.filtered_noise(x["H"], self.block_size, self.seed, offset, self.voice_offset, noise=noise)

@@ -25,9 +25,9 @@ N_FFTS = [2048, 1024, 512, 256, 128, 64]            # train/train.py:19
 class Zak(nn.Module):
     """Same attribute names as the reference's LightningModule: `model` (Decoder) and `loss` (MSSLoss)."""
 
-    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None, loss=None):
+    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None, loss=None, device_counter: bool = False):
         super().__init__()
-        self.model = Decoder(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth)
+        self.model = Decoder(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth, device_counter=device_counter)
         self.loss = loss if loss is not None else MSSLoss(N_FFTS)
 
     def forward(self, batch):
@@ -63,10 +63,19 @@ def allreduce_mean_(params, bucket_bytes: int = 25 << 20) -> int:
 
 class Trainer:
     def __init__(self, conf, device, amp: bool = False, lr: float = 1e-3, noise_seed: Optional[int] = None,
-                 voice_offset: int = 0, synth=None, loss=None):
+                 voice_offset: int = 0, synth=None, loss=None, graph: bool = False,
+                 device_counter: Optional[bool] = None):
+        """graph=True: the whole step (forward, backward, gradient all-reduce, Adam) is captured once as a CUDA graph on
+        the first call and replayed afterwards (fp32 only; batches are copied into static buffers)."""
         self.device = torch.device(device)
-        self.zak = Zak(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth, loss=loss).to(self.device)
-        self.opt = torch.optim.Adam(self.zak.parameters(), lr=lr)                        # train/train.py:22
+        self.graph = bool(graph) and self.device.type == "cuda" and not amp
+        self.zak = Zak(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth, loss=loss,
+                       device_counter=self.graph if device_counter is None else device_counter).to(self.device)
+        if self.graph:      # capturable Adam keeps step counts and the learning rate on the device
+            self.opt = torch.optim.Adam(self.zak.parameters(), lr=torch.tensor(lr, device=self.device), capturable=True)
+        else:
+            self.opt = torch.optim.Adam(self.zak.parameters(), lr=lr)                    # train/train.py:22
+        self._g = None
         self.sched = torch.optim.lr_scheduler.ReduceLROnPlateau(self.opt, patience=5)    # train/train.py:23
         self.amp = bool(amp) and self.device.type == "cuda"
         self.scaler = torch.amp.GradScaler("cuda", enabled=self.amp)
@@ -75,7 +84,54 @@ class Trainer:
             for p in self.zak.parameters():             # same initial weights everywhere
                 dist.broadcast(p.data, src=0)
 
+    def _graphed_step(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
+        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        params = list(self.zak.parameters())
+        if self._g is None:
+            self._static = {k: v.clone() for k, v in batch.items()}
+
+            def fwd_bwd():
+                loss = self.zak.training_loss(self._static)
+                loss.backward()
+                return loss.detach()
+
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(side):       # warm-up outside capture (allocator, cuDNN plans, twiddle tables, Adam state)
+                for _ in range(3):
+                    self.opt.zero_grad(set_to_none=True)
+                    fwd_bwd()
+                    allreduce_mean_(params)
+                    self.opt.step()
+            torch.cuda.current_stream(self.device).wait_stream(side)
+            torch.cuda.synchronize(self.device)
+            self.opt.zero_grad(set_to_none=True)            # gradients are (re)created inside the graph's memory pool
+            # Two graphs with the NCCL all-reduce between them (eager, on the same stream) when there are several ranks;
+            # with one rank the optimizer step is captured into the same graph.
+            self._g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._g):
+                self._loss = fwd_bwd()
+                if not multi:
+                    self.opt.step()
+            self._g_opt = None
+            if multi:
+                allreduce_mean_(params)
+                self._g_opt = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._g_opt, pool=self._g.pool()):
+                    self.opt.step()
+            self.steps += 3
+        for k, v in batch.items():
+            self._static[k].copy_(v)
+        self._g.replay()
+        if self._g_opt is not None:
+            allreduce_mean_(params)
+            self._g_opt.replay()
+        self.steps += 1
+        return self._loss
+
     def training_step(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
+        if self.graph:
+            return self._graphed_step(batch)
         self.opt.zero_grad(set_to_none=True)
         with torch.autocast("cuda", dtype=torch.float16, enabled=self.amp):
             loss = self.zak.training_loss(batch)

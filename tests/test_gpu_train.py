@@ -48,3 +48,24 @@ def test_training_step_matches_oracle_and_learns():
 
     losses = [float(tr.training_step(batch)) for _ in range(8)]
     assert all(l == l for l in losses) and losses[-1] < losses[0]
+
+
+def test_graphed_step_matches_eager():
+    """The CUDA-graph replay of the whole step (forward, backward, Adam) follows the eager step with the same noise."""
+    import test_train_gloo as H
+    from ddsp_pytorch_b200.train import Trainer, synthetic_batch
+    conf = H.small_conf()
+    conf.n_noise_filters, conf.hop_length, conf.sample_rate = 9, 64, 4000
+    torch.manual_seed(0)
+    tr = Trainer(conf, "cuda:0", noise_seed=3, graph=True)
+    tr.zak.loss = type(tr.zak.loss)([64, 128]).to("cuda:0")
+    graphed = [float(tr.training_step(synthetic_batch(conf, 3, "cuda:0", seed=10 + i))) for i in range(7)]
+    # the graphed trainer's first call runs three eager warm-up steps on its first batch before the captured one
+    torch.manual_seed(0)
+    tr_e = Trainer(conf, "cuda:0", noise_seed=3, graph=False, device_counter=True)
+    tr_e.zak.loss = type(tr_e.zak.loss)([64, 128]).to("cuda:0")
+    first = synthetic_batch(conf, 3, "cuda:0", seed=10)
+    want = [float(tr_e.training_step(first)) for _ in range(4)][-1:]
+    want += [float(tr_e.training_step(synthetic_batch(conf, 3, "cuda:0", seed=10 + i))) for i in range(1, 7)]
+    for g, w in zip(graphed, want):
+        assert abs(g - w) <= 2e-3 * abs(w), (graphed, want)
