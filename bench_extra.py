@@ -7,6 +7,7 @@ contract).  One JSON line per workload:
   mss     cfg 5: MSS loss alone, FFT sizes 2048..64 on 64 x 4 s @ 16 kHz clips, forward + backward
   reverb  cfg 1' shapes (B=16, N=88064, L=44100) and a large batch (B=256, N=192000, L=48000): fwd + bwd (gx, gir)
   path    cfg 1': oscillator + noise + reverb + 6-scale MSS, forward + backward through the module API
+  ctrl    row X1: fused Controller tail vs the torch expression at cfg 2's shapes
   rt      cfg 3: OscillatorBank.live + FilteredNoise + Reverb.live_forward per 2048-sample block, p50/p99 latency
 No CPU fallback: needs the CUDA library and a GPU.
 """
@@ -169,6 +170,40 @@ def bench_fft(args, dev):
     return out
 
 
+def bench_ctrl(args, dev):
+    """Row X1: the Controller tail (three Linear heads + modified_sigmoid) as the fused kernel vs the torch expression
+    (cuBLAS fp32 + elementwise kernels), forward and forward+backward, at cfg 2's shapes."""
+    from ddsp_pytorch_b200 import ops
+    from ddsp_pytorch_b200.controller import modified_sigmoid
+    out = []
+    U, K, NB = 512, 180, 195
+    for B, T in ((32, 172), (4, 172)):
+        x = torch.randn(B, T, U, device=dev, requires_grad=True)
+        heads = [torch.nn.Linear(U, n).to(dev) for n in (K, 1, NB)]
+        ps = [t for h in heads for t in (h.weight, h.bias)]
+        gs = [torch.randn(B, T, n, device=dev) for n in (K, 1, NB)]
+
+        def fused(bwd):
+            c, a, H = ops.controller_heads(x, *ps)
+            if bwd:
+                torch.autograd.backward((c, a, H), gs)
+
+        def stock(bwd):
+            c, a, H = (modified_sigmoid(h(x)) for h in heads)
+            if bwd:
+                torch.autograd.backward((c, a, H), gs)
+
+        R, J = B * T, K + 1 + NB
+        res = {"workload": f"controller tail R={R} U={U} J={J}", "flop_fwd": 2.0 * R * U * J}
+        for name, fn in (("fused", fused), ("torch", stock)):
+            with torch.no_grad():
+                res[f"{name}_fwd_ms"] = ev_time(lambda: fn(False), args.reps)
+            res[f"{name}_fwd_bwd_ms"] = ev_time(lambda: fn(True), args.reps)
+        res["fused_fwd_TFLOPs"] = res["flop_fwd"] / (res["fused_fwd_ms"] * 1e-3) / 1e12
+        out.append(res)
+    return out
+
+
 def main():
     p = argparse.ArgumentParser()
     p.add_argument("--workloads", default="mss,reverb,path,rt")
@@ -179,7 +214,7 @@ def main():
         raise RuntimeError("bench_extra.py needs a CUDA device; there is no CPU fallback")
     dev = torch.device("cuda", 0)
     torch.manual_seed(0)
-    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt}
+    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt, "ctrl": bench_ctrl}
     for w in args.workloads.split(","):
         res = table[w](args, dev)
         for r in (res if isinstance(res, list) else [res]):

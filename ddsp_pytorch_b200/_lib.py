@@ -37,6 +37,10 @@ SIGNATURES = {
     "ddsp_mss_count": (C.c_int64, [_i, _i, _i, _i]),
     "ddsp_mss_forward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, C.c_float, C.c_float, _i, _i, _p]),
     "ddsp_mss_backward": (_i, [_p, _p, _p, _i, _i, _p]),
+    "ddsp_ctrl_heads_ldz": (_i, [_i, _i]),
+    "ddsp_ctrl_heads_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "ddsp_ctrl_heads_forward": (_i, [_p] * 11 + [_i, _i, _i, _i, _p]),
+    "ddsp_ctrl_heads_backward": (_i, [_p] * 16 + [_i, _i, _i, _i, _p]),
     "ddsp_loudness_frames": (_i, [_i, _i, _i]),
     "ddsp_loudness_forward": (_i, [_p, _p, _p, _i, _i, _i, _i, _p]),
     "ddsp_fft_c2c": (_i, [_p, _p, _i, C.c_longlong, _i, _i, _p]),

@@ -11,6 +11,7 @@ from __future__ import annotations
 import torch
 import torch.nn as nn
 
+from . import ops
 from .modules import FilteredNoise, OscillatorBank, Reverb
 
 
@@ -37,9 +38,15 @@ class MLP(nn.Module):
 
 
 class Controller(nn.Module):
-    def __init__(self, conf):
+    """decoder.py:41-116.  The tail -- three Linear heads + modified_sigmoid -- runs as one fused kernel
+    (`ops.controller_heads`) whenever its input is a CUDA tensor; the parameters stay the three
+    nn.Linear modules of the reference, so state dicts are unchanged.  On CPU tensors (the gloo tests) the plain torch
+    expression is used -- that is host-side test plumbing, not a product path."""
+
+    def __init__(self, conf, fused_tail: bool = True):
         super().__init__()
         self.config = conf
+        self.fused_tail = bool(fused_tail)
         u, layers = conf.decoder_mlp_units, conf.decoder_mlp_layers
         self.mlp_f0 = MLP(1, u, layers)
         self.mlp_loudness = MLP(1, u, layers)
@@ -57,8 +64,12 @@ class Controller(nn.Module):
         x = torch.cat((lf0, lld), dim=-1)
         x, h = self.gru(x) if hidden is None else self.gru(x, hidden)
         x = self.mlp_gru(torch.cat((x, lf0, lld), dim=-1))
-        controls = dict(f0=batch["f0"], c=modified_sigmoid(self.dense_harmonic(x)), hidden=h,
-                        H=modified_sigmoid(self.dense_filter(x)), a=modified_sigmoid(self.dense_loudness(x)))
+        if self.fused_tail and x.is_cuda:
+            c, a, H = ops.controller_heads(x, self.dense_harmonic.weight, self.dense_harmonic.bias, self.dense_loudness.weight,
+                                           self.dense_loudness.bias, self.dense_filter.weight, self.dense_filter.bias)
+        else:
+            c, a, H = (modified_sigmoid(head(x)) for head in (self.dense_harmonic, self.dense_loudness, self.dense_filter))
+        controls = dict(f0=batch["f0"], c=c, hidden=h, H=H, a=a)
         if hidden is not None:
             return controls, hidden                     # the reference returns the INPUT hidden state here (decoder.py:106-107)
         return controls

@@ -334,3 +334,57 @@ def loudness(signal: torch.Tensor, a_weight: torch.Tensor, n_fft: int, hop: int)
         out = torch.empty(B, max(F_, 0), 1, dtype=torch.float32, device=x.device)
         _lib.call("ddsp_loudness_forward", x.data_ptr(), aw.data_ptr(), out.data_ptr(), B, N, n_fft, hop, _stream())
     return out
+
+
+class _ControllerHeads(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w_c, b_c, w_a, b_a, w_h, b_h):
+        x_ = _f32(x)
+        params = [_f32(p) for p in (w_c, b_c, w_a, b_a, w_h, b_h)]
+        U = x_.shape[-1]
+        K, NB = params[0].shape[0], params[4].shape[0]
+        if params[0].shape[1] != U or params[2].shape != (1, U) or params[4].shape[1] != U:
+            raise RuntimeError(f"controller_heads: weights {tuple(w_c.shape)}/{tuple(w_a.shape)}/{tuple(w_h.shape)} do not "
+                               f"match the {U}-wide input")
+        lead = x_.shape[:-1]
+        R = x_.numel() // U
+        dev = x_.device
+        need_grad = any(t.requires_grad for t in (x, w_c, b_c, w_a, b_a, w_h, b_h))
+        with torch.cuda.device(dev):
+            lib = _lib.load()
+            c = torch.empty(*lead, K, dtype=torch.float32, device=dev)
+            a = torch.empty(*lead, 1, dtype=torch.float32, device=dev)
+            H = torch.empty(*lead, NB, dtype=torch.float32, device=dev)
+            z = torch.empty(R, lib.ddsp_ctrl_heads_ldz(K, NB), dtype=torch.float32, device=dev) if need_grad else None
+            _lib.call("ddsp_ctrl_heads_forward", x_.data_ptr(), *(p.data_ptr() for p in params), c.data_ptr(), a.data_ptr(),
+                      H.data_ptr(), z.data_ptr() if z is not None else None, R, U, K, NB, _stream())
+        if need_grad:
+            ctx.save_for_backward(x_, params[0], params[2], params[4], z)
+            ctx.dims = (R, U, K, NB)
+            ctx.meta = (x.shape, x.dtype, x.requires_grad, [p.dtype for p in (w_c, b_c, w_a, b_a, w_h, b_h)])
+        return c, a, H
+
+    @staticmethod
+    def backward(ctx, g_c, g_a, g_h):
+        x_, w_c, w_a, w_h, z = ctx.saved_tensors
+        R, U, K, NB = ctx.dims
+        x_shape, x_dtype, x_req, pdt = ctx.meta
+        dev = x_.device
+        gs = [None if g is None else _f32(g) for g in (g_c, g_a, g_h)]
+        with torch.cuda.device(dev):
+            lib = _lib.load()
+            mk = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)  # noqa: E731
+            gx = mk(R, U) if x_req else None
+            outs = [mk(K, U), mk(K), mk(1, U), mk(1), mk(NB, U), mk(NB)]
+            ws = _bytes(lib.ddsp_ctrl_heads_workspace_bytes(R, U, K, NB), dev)
+            _lib.call("ddsp_ctrl_heads_backward", x_.data_ptr(), w_c.data_ptr(), w_a.data_ptr(), w_h.data_ptr(), z.data_ptr(),
+                      *(None if g is None else g.data_ptr() for g in gs), None if gx is None else gx.data_ptr(),
+                      *(o.data_ptr() for o in outs), ws.data_ptr(), R, U, K, NB, _stream())
+        gx = None if gx is None else gx.view(x_shape).to(x_dtype)
+        return (gx, *(o.to(d) for o, d in zip(outs, pdt)))
+
+
+def controller_heads(x, w_c, b_c, w_a, b_a, w_h, b_h):
+    """x [..,U] -> (c [..,K], a [..,1], H [..,NB]) = modified_sigmoid of the three Linear heads (decoder.py:96-100,110-116)
+    in one launch, fp32 outputs in the layout the synthesis kernels read; nn.Linear weight layout [out,in]."""
+    return _ControllerHeads.apply(x, w_c, b_c, w_a, b_a, w_h, b_h)

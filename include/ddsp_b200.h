@@ -170,6 +170,27 @@ int ddsp_loudness_forward(const float* x, const float* a_weight, float* out, int
                           int hop, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Controller tail  --  Controller.forward, model/autoencoder/decoder.py:96-100 with the heads of
+ * :74-76 and modified_sigmoid :110-116:
+ *   c[R,K] = msig(x W_c^T + b_c), a[R,1] = msig(x W_a^T + b_a), H[R,NB] = msig(x W_h^T + b_h),
+ *   msig(z) = 2 sigmoid(z)^2.3026 + 1e-7, x [R,U] (R = B*T rows of the last MLP's output), nn.Linear
+ *   weight layout [out,in].  One launch; U % 4 == 0; matrices 16-byte aligned.
+ *   z (optional) [R, ddsp_ctrl_heads_ldz(K,NB)] receives the pre-activations for the backward call.
+ * backward: from g_c, g_a, g_h (any may be NULL = zero) to gx [R,U] (NULL to skip) and the six
+ *   parameter gradients (overwritten, not accumulated); deterministic (fixed summation order).
+ *   workspace: ddsp_ctrl_heads_workspace_bytes(R,U,K,NB) bytes, 16-byte aligned.
+ * ------------------------------------------------------------------------------------------ */
+int ddsp_ctrl_heads_ldz(int K, int NB);
+size_t ddsp_ctrl_heads_workspace_bytes(int R, int U, int K, int NB);
+int ddsp_ctrl_heads_forward(const float* x, const float* w_c, const float* b_c, const float* w_a,
+                            const float* b_a, const float* w_h, const float* b_h, float* c, float* a,
+                            float* H, float* z, int R, int U, int K, int NB, void* stream);
+int ddsp_ctrl_heads_backward(const float* x, const float* w_c, const float* w_a, const float* w_h,
+                             const float* z, const float* g_c, const float* g_a, const float* g_h,
+                             float* gx, float* gw_c, float* gb_c, float* gw_a, float* gb_a, float* gw_h,
+                             float* gb_h, void* workspace, int R, int U, int K, int NB, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * The transform underneath the reverb and the spectral loss, on its own: `batch` complex FFTs of
  * size n (power of two in [8,4096]), interleaved (re,im) fp32 (fp64 = 0) or fp64 (fp64 != 0), in
  * natural order; inverse != 0 is the unnormalised inverse.  Replaces the cuFFT calls the reference

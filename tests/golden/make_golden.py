@@ -190,8 +190,56 @@ def path_case(name, B, T, K, NB, sr, hop, seed):
     print(name, "loss64 =", float(loss))
 
 
+def ctrl_heads_case(name, B, T, U, K, NB, seed):
+    """The reference's own Controller (decoder.py:41-116), fp64: the input of its three heads (output of mlp_gru, taken
+    with a forward hook), the head parameters, c / a / H and the gradients of a random linear functional of them."""
+    from model.autoencoder.decoder import Controller
+    torch.manual_seed(seed)
+    cf = SimpleNamespace(n_harmonics=K, n_noise_filters=NB, decoder_mlp_units=U, decoder_mlp_layers=2,
+                         decoder_gru_units=U, decoder_gru_layers=1)
+    ctl = Controller(cf)
+    with torch.no_grad():       # spread the pre-activations so both tails of the sigmoid are exercised
+        for head in (ctl.dense_harmonic, ctl.dense_loudness, ctl.dense_filter):
+            head.weight.mul_(6.0)
+            head.bias.add_(torch.randn_like(head.bias))
+            head.weight.copy_(head.weight.float())      # fp32-representable parameters
+            head.bias.copy_(head.bias.float())
+    ctl = ctl.double()
+    seen = {}
+
+    def hook(_m, _inp, out):
+        out.retain_grad()
+        seen["x"] = out
+    ctl.mlp_gru.register_forward_hook(hook)
+    batch = dict(normalized_cents=torch.rand(B, T, 1, dtype=torch.float64), loudness=torch.rand(B, T, 1, dtype=torch.float64),
+                 f0=torch.rand(B, T, 1, dtype=torch.float64) * 300 + 80)
+    out = ctl(batch)
+    # the fp32 kernel sees the fp32 rounding of the latent: re-run the heads on that so the pin is exact
+    x = seen["x"].detach().float().double().requires_grad_(True)
+    c = ctl.modified_sigmoid(ctl.dense_harmonic(x))
+    a = ctl.modified_sigmoid(ctl.dense_loudness(x))
+    H = ctl.modified_sigmoid(ctl.dense_filter(x))
+    assert torch.allclose(c, out["c"], atol=1e-6) and torch.allclose(H, out["H"], atol=1e-6)
+    g = [torch.randn_like(t).float().double() for t in (c, a, H)]
+    for p_ in ctl.parameters():
+        p_.grad = None
+    ((c * g[0]).sum() + (a * g[1]).sum() + (H * g[2]).sum()).backward()
+    np.savez_compressed(os.path.join(HERE, name), B=B, T=T, U=U, K=K, NB=NB, x=f32(x),
+                        w_c=f32(ctl.dense_harmonic.weight), b_c=f32(ctl.dense_harmonic.bias),
+                        w_a=f32(ctl.dense_loudness.weight), b_a=f32(ctl.dense_loudness.bias),
+                        w_h=f32(ctl.dense_filter.weight), b_h=f32(ctl.dense_filter.bias),
+                        c=f64(c), a=f64(a), H=f64(H), g_c=f32(g[0]), g_a=f32(g[1]), g_h=f32(g[2]), gx=f64(x.grad),
+                        gw_c=f64(ctl.dense_harmonic.weight.grad), gb_c=f64(ctl.dense_harmonic.bias.grad),
+                        gw_a=f64(ctl.dense_loudness.weight.grad), gb_a=f64(ctl.dense_loudness.bias.grad),
+                        gw_h=f64(ctl.dense_filter.weight.grad), gb_h=f64(ctl.dense_filter.bias.grad))
+    print(name, "c range", float(c.min()), float(c.max()))
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
+    if len(sys.argv) > 1 and sys.argv[1] == "ctrl":     # only the controller-tail fixtures (added with row X1)
+        ctrl_heads_case("ref_ctrl_heads.npz", B=3, T=50, U=64, K=21, NB=13, seed=14)   # R=150: ragged tiles, J=35 (ld 36)
+        sys.exit(0)
     osc_case("ref_osc_small.npz", B=2, T=6, K=24, sr=16000, hop=64, seed=1)
     osc_case("ref_osc_default.npz", B=1, T=8, K=180, sr=44100, hop=512, seed=2)
     # high pitch: most harmonics masked, some frames cross Nyquist between neighbours
@@ -208,3 +256,4 @@ if __name__ == "__main__":
     reverb_live_case("ref_reverb_live.npz", sr=1000, block=256, calls=3, seed=11)
     mss_case("ref_mss.npz", B=2, N=4096, n_ffts=[2048, 1024, 512, 256, 128, 64], seed=12)
     path_case("ref_path.npz", B=2, T=12, K=20, NB=17, sr=4000, hop=64, seed=13)
+    ctrl_heads_case("ref_ctrl_heads.npz", B=3, T=50, U=64, K=21, NB=13, seed=14)
