@@ -199,7 +199,7 @@ def run_b200(args):
     import torch.distributed as dist
     import ddsp_pytorch_b200 as d
     from ddsp_pytorch_b200 import _lib, ops
-    from oracle import ddsp_oracle as O            # input generator only (synthetic_controls); never on the timed path
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -218,7 +218,7 @@ def run_b200(args):
     conf = d.Config(sample_rate=sr, hop_length=hop, n_harmonics=K, n_noise_filters=NB)
 
     # ---- synthetic inputs, generated on the host, this rank's voices only ------------
-    f0h, ch, ah, Hh = O.synthetic_controls(Bl, T, K, NB, sr, hop, seed=1234 + 4, voice_offset=v_lo)
+    f0h, ch, ah, Hh = synthetic_controls(Bl, T, K, NB, sr, hop, seed=1234 + 4, voice_offset=v_lo)
     gh = torch.randn(Bl, N, generator=torch.Generator().manual_seed(99 + rank))
     host = [t.pin_memory() for t in (f0h, ch, ah, Hh, gh)]
     f0, c, a, H, g = (t.to(dev) for t in host)
@@ -369,6 +369,12 @@ def run_b200(args):
         if world > 1:
             dist.destroy_process_group()
         return
+    rt = None
+    if world == 1:      # BASELINE metric, third part: real-time block latency (cfg 3), a 1-second side measurement
+        import types
+        import bench_extra
+        r = bench_extra.bench_rt(types.SimpleNamespace(rt_calls=500), dev)
+        rt = {k: r[k] for k in ("workload", "deadline_ms", "host_p50_ms", "host_p99_ms", "device_p50_ms", "device_p99_ms")}
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         r = cpu_measure(args, sh, steps=2, warmup=1)
@@ -376,7 +382,7 @@ def run_b200(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args, sh), "clocks": clocks, "e2e": e2e, "gpu_launches": 6 * args.steps,
-            "roofline": roofline, "roofline_fused": fused, "cpu_baseline": cpu, "kernels_ms": kernels_ms, "fp32_fma_peak_tflops_measured": fp32_peak}
+            "roofline": roofline, "roofline_fused": fused, "cpu_baseline": cpu, "kernels_ms": kernels_ms, "fp32_fma_peak_tflops_measured": fp32_peak, "rt_block_latency": rt}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

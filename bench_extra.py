@@ -97,12 +97,12 @@ def bench_reverb(args, dev):
 def bench_path(args, dev):
     """cfg 1' (shipped config/default.py): decoder tail exactly as decoder.py:129-133 + MSSLoss, fwd+bwd."""
     import ddsp_pytorch_b200 as d
-    from oracle import ddsp_oracle as O            # input generator only
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
     conf = d.SHIPPED
     B, sr, hop, K, NB = 16, conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters
     T = 172
     N = T * hop
-    f0, c, a, H = (t.to(dev) for t in O.synthetic_controls(B, T, K, NB, sr, hop, seed=1234 + 1))
+    f0, c, a, H = (t.to(dev) for t in synthetic_controls(B, T, K, NB, sr, hop, seed=1234 + 1))
     target = (torch.randn(B, N, generator=torch.Generator().manual_seed(9)) * 0.1).clamp(-1, 1).to(dev)
     bank, fn, rv = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=7), d.Reverb(conf).to(dev)
     loss_fn = d.MSSLoss([2048, 1024, 512, 256, 128, 64]).to(dev)
@@ -123,13 +123,13 @@ def bench_path(args, dev):
 def bench_rt(args, dev):
     """cfg 3 (rt/synth.py:23, autoencoder.py:26-32): one 2048-sample block = 4 frames, batch 1, live path."""
     import ddsp_pytorch_b200 as d
-    from oracle import ddsp_oracle as O
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
     conf = d.SHIPPED
     sr, hop, K, NB, T = conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters, 4
     bank, fn, rv = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=7), d.Reverb(conf).to(dev)
     ctrls = []
     for i in range(16):
-        f0, c, a, H = (t.to(dev) for t in O.synthetic_controls(1, T, K, NB, sr, hop, seed=50 + i))
+        f0, c, a, H = (t.to(dev) for t in synthetic_controls(1, T, K, NB, sr, hop, seed=50 + i))
         ctrls.append({"f0": f0, "c": c, "a": a, "H": H})
     n_calls = args.rt_calls
     host_ms, dev_ms = [], []

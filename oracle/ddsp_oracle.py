@@ -310,13 +310,9 @@ def loudness_encoder(signal: torch.Tensor, a_weight: torch.Tensor, n_fft: int, h
 # ----------------------------------------------------------------------------------------------
 # Controller tail -- model/autoencoder/decoder.py:96-100 with modified_sigmoid :110-116
 # ----------------------------------------------------------------------------------------------
-def modified_sigmoid(z: torch.Tensor) -> torch.Tensor:
-    """decoder.py:110-116: sigmoid -> pow(2.3026) -> mul(2) -> add(1e-7)."""
-    return torch.sigmoid(z).pow(2.3026) * 2.0 + 1e-7
-
-
 def controller_heads(x, w_c, b_c, w_a, b_a, w_h, b_h):
     """The three Linear heads on the last MLP's output and their activation (decoder.py:74-76, 96-100):
-    c = msig(x W_c^T + b_c), a = msig(x W_a^T + b_a), H = msig(x W_h^T + b_h); nn.Linear weight layout [out,in]."""
+    c = msig(x W_c^T + b_c), a = msig(x W_a^T + b_a), H = msig(x W_h^T + b_h), msig = `modified_sigmoid` above
+    (decoder.py:110-116: sigmoid -> pow(2.3026) -> mul(2) -> add(1e-7)); nn.Linear weight layout [out,in]."""
     lin = torch.nn.functional.linear
     return modified_sigmoid(lin(x, w_c, b_c)), modified_sigmoid(lin(x, w_a, b_a)), modified_sigmoid(lin(x, w_h, b_h))

@@ -58,3 +58,13 @@ def test_voice_shard_covers_everything():
             assert ranges[0][0] == 0 and ranges[-1][1] == B
             assert all(ranges[i][1] == ranges[i + 1][0] for i in range(world - 1))
             assert max(h - l for l, h in ranges) - min(h - l for l, h in ranges) <= 1
+
+
+def test_package_input_generator_draws_the_oracle_voices():
+    """bench.py generates its inputs with ddsp_pytorch_b200.synthetic (the product arm never imports oracle/); the values
+    are the oracle generator's, for any sharding."""
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
+    from oracle import ddsp_oracle as O
+    want = O.synthetic_controls(3, 7, 5, 4, 16000, 64, seed=9, voice_offset=2)
+    got = synthetic_controls(3, 7, 5, 4, 16000, 64, seed=9, voice_offset=2)
+    assert all(torch.equal(a, b) for a, b in zip(got, want))
