@@ -310,6 +310,12 @@ constexpr int TEAM_BLOCK = 128;
 
 __device__ __forceinline__ int swz(int i) { return i + ((i >> 5) << 2); }
 
+// A team's shared memory is private to it: when the team is exactly one warp (hop 512) a warp barrier is enough, and the
+// four frames of a CTA drift apart so one frame's FMA-bound convolution overlaps another's latency-bound tap build.
+__device__ __forceinline__ void team_sync(int TS) {
+    if (TS == 32) __syncwarp(); else __syncthreads();
+}
+
 struct TeamLayout {
     int half, TP, PADL, uc_off, n_H, n_rr, n_u, n_uc, n_cor, total;
 };
@@ -325,50 +331,72 @@ __host__ __device__ inline TeamLayout team_layout(int NB, int hop) {
     L.n_u = (logical + ((logical >> 5) << 2) + 4 + 3) & ~3;
     L.n_uc = (2 * L.half + 4 + 3) & ~3;                 // unswizzled copy of u[-half .. half) for the corner
     L.n_cor = (L.half + 3) & ~3;
-    L.total = L.n_H + L.n_rr + 2 * L.TP + L.n_u + L.n_uc + L.n_cor;
+    L.total = L.n_H + L.n_rr + 3 * L.TP + 4 + L.n_u + L.n_uc + L.n_cor;      // taps: two pair-swapped copies + wrapped + tap 0
     const int out_need = hop;                           // the output staging area reuses the u region
     if (L.n_u < out_need) L.total += out_need - L.n_u;
     return L;
 }
 
-// r[0..half] from H (team-cooperative); H, rr in shared memory.
+// r[0..half] from H (team-cooperative); H, rr in shared memory (H 16-byte aligned, readable up to the next multiple of 4).
+// Lane j handles r[j] and r[half-j] for j < half/2; the middle tap (theta = pi/2: cos(m pi/2) is 0, +-1) would cost the
+// whole team a second pass for one lane, so it is summed directly instead.
 __device__ __forceinline__ void team_build_r(const float* H, float* rr, int NB, int l, int TS) {
     const int half = NB - 1, M = 2 * half;
     const float invM = 1.0f / (float)M;
-    for (int j = l; 2 * j <= half; j += TS) {
-        const float sh = sinpif((float)j * invM);       // sin(theta/2), theta = 2 pi j / M <= pi/2
+    const float h0 = H[0], hN = H[half];
+    for (int j = l; 2 * j < half; j += TS) {
+        const float sh = sinpif((float)j * invM);       // sin(theta/2), theta = 2 pi j / M < pi/2
         const float dl = -4.f * sh * sh;                // 2 cos(theta) - 2
         float e = 0.5f * dl, c = 1.f + e;               // cos(1*theta)
         float E = 0.f, O = 0.f;
-        int m = 1;
-        for (; m + 1 < half; m += 2) {
-            O = fmaf(H[m], c, O);
-            e = fmaf(dl, c, e); c += e;
-            E = fmaf(H[m + 1], c, E);
-            e = fmaf(dl, c, e); c += e;
+        for (int m4 = 0; m4 < half; m4 += 4) {
+            const float4 h = *reinterpret_cast<const float4*>(H + m4);
+            const float hv[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int m = m4 + k;
+                if (m == 0 || m >= half) continue;
+                if (m & 1) O = fmaf(hv[k], c, O); else E = fmaf(hv[k], c, E);
+                e = fmaf(dl, c, e); c += e;
+            }
         }
-        if (m < half) O = fmaf(H[m], c, O);
-        const float h0 = H[0], hN = H[half];
         const float sj = (j & 1) ? -hN : hN, sk = ((half - j) & 1) ? -hN : hN;
         rr[j] = (h0 + sj + 2.f * (E + O)) * invM;
         rr[half - j] = (h0 + sk + 2.f * (E - O)) * invM;
     }
+    if ((half & 1) == 0 && l == (half / 2) % TS) {      // j = half/2
+        float E = 0.f;
+        for (int m = 2; m < half; m += 4) E -= H[m];    // cos(m pi/2) = -1 at m = 2, 6, ..
+        for (int m = 4; m < half; m += 4) E += H[m];    //              +1 at m = 4, 8, ..
+        const float sj = ((half / 2) & 1) ? -hN : hN;
+        rr[half / 2] = (h0 + sj + 2.f * E) * invM;
+    }
 }
 
-#define NOISE_TILE(NW, M1, M2, Q0)                                                                              \
+// Packed tile: 16 outputs x 8 taps as 64 FFMA2.  Every output keeps TWO partial sums (one per lane of a float2) so that
+// a tap pair (h[a], h[a+1]) meets an ascending, even-aligned window pair (w[x], w[x+1]):
+//   odd  r : taps (q0+2k, q0+2k+1)   x window pair starting at 7+r-2k -> tap operand (h[2k+1], h[2k])   = copy A
+//   even r : taps (q0+2k+1, q0+2k+2) x window pair starting at 6+r-2k -> tap operand (h[2k+2], h[2k+1]) = copy B
+// i.e. even outputs run one tap behind: tap 0 is added before the loop and tap TP (zero) closes the last tile.
+#define NOISE_TILE2(NW, M1, M2, Q0)                                                                             \
     {                                                                                                           \
         const float4 l0_ = *reinterpret_cast<const float4*>(u + swz(ub - (Q0) - 8));                            \
         const float4 l1_ = *reinterpret_cast<const float4*>(u + swz(ub - (Q0) - 4));                            \
-        NW[0] = l0_.x; NW[1] = l0_.y; NW[2] = l0_.z; NW[3] = l0_.w;                                             \
-        NW[4] = l1_.x; NW[5] = l1_.y; NW[6] = l1_.z; NW[7] = l1_.w;                                             \
-        const float4 t0_ = *reinterpret_cast<const float4*>(taps + (Q0));                                       \
-        const float4 t1_ = *reinterpret_cast<const float4*>(taps + (Q0) + 4);                                   \
-        const float tp_[8] = {t0_.x, t0_.y, t0_.z, t0_.w, t1_.x, t1_.y, t1_.z, t1_.w};                          \
-        _Pragma("unroll") for (int d = 0; d < 8; ++d) {                                                         \
+        NW[0] = make_float2(l0_.x, l0_.y); NW[1] = make_float2(l0_.z, l0_.w);                                   \
+        NW[2] = make_float2(l1_.x, l1_.y); NW[3] = make_float2(l1_.z, l1_.w);                                   \
+        const float4 a0_ = *reinterpret_cast<const float4*>(hcA + (Q0));                                        \
+        const float4 a1_ = *reinterpret_cast<const float4*>(hcA + (Q0) + 4);                                    \
+        const float4 b0_ = *reinterpret_cast<const float4*>(hcB + (Q0));                                        \
+        const float4 b1_ = *reinterpret_cast<const float4*>(hcB + (Q0) + 4);                                    \
+        const float2 A2_[4] = {make_float2(a0_.x, a0_.y), make_float2(a0_.z, a0_.w), make_float2(a1_.x, a1_.y), \
+                               make_float2(a1_.z, a1_.w)};                                                      \
+        const float2 B2_[4] = {make_float2(b0_.x, b0_.y), make_float2(b0_.z, b0_.w), make_float2(b1_.x, b1_.y), \
+                               make_float2(b1_.z, b1_.w)};                                                      \
+        _Pragma("unroll") for (int k = 0; k < 4; ++k) {                                                         \
             _Pragma("unroll") for (int r = 0; r < 16; ++r) {                                                    \
-                const int ix = 8 + r - d;                                                                       \
-                const float wv = ix < 8 ? NW[ix] : (ix < 16 ? M1[ix - 8] : M2[ix - 16]);                        \
-                acc[r] = fmaf(tp_[d], wv, acc[r]);                                                              \
+                const int pi = ((r & 1) ? 7 + r - 2 * k : 6 + r - 2 * k) >> 1;                                  \
+                const float2 wv = pi < 4 ? NW[pi] : (pi < 8 ? M1[pi - 4] : M2[pi - 8]);                         \
+                acc2[r] = __ffma2_rn((r & 1) ? A2_[k] : B2_[k], wv, acc2[r]);                                   \
             }                                                                                                   \
         }                                                                                                       \
     }
@@ -390,9 +418,11 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
     float* base = smem + (size_t)team * L.total;
     float* Hs = base;
     float* rr = Hs + L.n_H;
-    float* hc = rr + L.n_rr;
-    float* ha = hc + L.TP;
-    float* u = ha + L.TP;                               // swizzled: logical index PADL + j
+    float* hcA = rr + L.n_rr;                           // causal taps, pairs swapped: (h1,h0,h3,h2,..)
+    float* hcB = hcA + L.TP;                            // causal taps, one behind:    (h2,h1,h4,h3,..,0,h[TP-1])
+    float* ha = hcB + L.TP;                             // wrapped taps
+    float* h0s = ha + L.TP;                             // h[0]
+    float* u = h0s + 4;                                 // swizzled: logical index PADL + j
     float* uc = u + (L.n_u < hop ? hop : L.n_u);        // uc[half + x] = u[x], x in [-half, half)
     float* cor = uc + L.n_uc;
     const int half = L.half, TP = L.TP, PADL = L.PADL;
@@ -405,7 +435,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
         for (int m = l; m < NB; m += TS) Hs[m] = H[frame * NB + m];
     for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
     for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
-    __syncthreads();
+    team_sync(TS);
     if (live) {
         const float* nf = noise ? noise + frame * hop : nullptr;
         for (int q = l; q < (hop >> 2); q += TS) {
@@ -420,7 +450,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
         }
         team_build_r(Hs, rr, NB, l, TS);
     }
-    __syncthreads();
+    team_sync(TS);
     // ---- stage 2: windowed taps (filtered_noise.py:14-20) -----------------------------------------
     if (live) {
         const float invM = 0.5f / (float)half;
@@ -431,41 +461,63 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
                 c = rr[q] * (0.5f + 0.5f * cq);
                 a = rr[half - q] * (0.5f - 0.5f * cq);
             }
-            hc[q] = c;
+            hcA[q ^ 1] = c;
+            if (q & 1) hcB[q] = c;
+            else if (q >= 2) hcB[q - 2] = c;
+            else { h0s[0] = c; hcB[TP - 2] = 0.f; }
             ha[q] = a;
         }
     }
-    __syncthreads();
+    team_sync(TS);
     // ---- stage 3: causal taps, 16 outputs per thread ----------------------------------------------
     float acc[16];
 #pragma unroll
     for (int r = 0; r < 16; ++r) acc[r] = 0.f;
     if (live) {
         const int ub = PADL + 16 * l;                   // logical index of this thread's first output
-        float wa[8], wb[8], wc[8];
+        float2 acc2[16];
+        float2 wa[4], wb[4], wc[4];
         {
             const float4 a0 = *reinterpret_cast<const float4*>(u + swz(ub)), a1 = *reinterpret_cast<const float4*>(u + swz(ub + 4));
             const float4 a2 = *reinterpret_cast<const float4*>(u + swz(ub + 8)), a3 = *reinterpret_cast<const float4*>(u + swz(ub + 12));
-            wb[0] = a0.x; wb[1] = a0.y; wb[2] = a0.z; wb[3] = a0.w; wb[4] = a1.x; wb[5] = a1.y; wb[6] = a1.z; wb[7] = a1.w;
-            wc[0] = a2.x; wc[1] = a2.y; wc[2] = a2.z; wc[3] = a2.w; wc[4] = a3.x; wc[5] = a3.y; wc[6] = a3.z; wc[7] = a3.w;
+            wb[0] = make_float2(a0.x, a0.y); wb[1] = make_float2(a0.z, a0.w); wb[2] = make_float2(a1.x, a1.y); wb[3] = make_float2(a1.z, a1.w);
+            wc[0] = make_float2(a2.x, a2.y); wc[1] = make_float2(a2.z, a2.w); wc[2] = make_float2(a3.x, a3.y); wc[3] = make_float2(a3.z, a3.w);
+            const float h0 = h0s[0];                    // tap 0 of the even outputs (they run one tap behind)
+#pragma unroll
+            for (int r = 0; r < 16; r += 2) {
+                const float2 own = (r < 8) ? wb[r >> 1] : wc[(r - 8) >> 1];
+                acc2[r] = make_float2(h0 * own.x, 0.f);
+                acc2[r + 1] = make_float2(0.f, 0.f);
+            }
         }
-        const float* taps = hc;
         for (int q0 = 0; q0 < TP; q0 += 24) {
-            NOISE_TILE(wa, wb, wc, q0);
+            NOISE_TILE2(wa, wb, wc, q0);
             if (q0 + 8 >= TP) break;
-            NOISE_TILE(wc, wa, wb, q0 + 8);
+            NOISE_TILE2(wc, wa, wb, q0 + 8);
             if (q0 + 16 >= TP) break;
-            NOISE_TILE(wb, wc, wa, q0 + 16);
+            NOISE_TILE2(wb, wc, wa, q0 + 16);
         }
+#pragma unroll
+        for (int r = 0; r < 16; ++r) acc[r] = acc2[r].x + acc2[r].y;
         // ---- stage 4: wrapped taps, one corner output per thread per pass -------------------------
+        // u[x] = 0 for x < 0: output jp only sees taps i <= jp; the bound is rounded up to the pass so it stays team-uniform
         for (int jp = l; jp < half; jp += TS) {
             float a2 = 0.f;
             const float* ux = uc + half + jp;
-            for (int i = 0; i < half; ++i) a2 = fmaf(ha[i], ux[-i], a2);
+            const int iend = min(half, (jp - l) + TS);
+            int i = 0;
+            for (; i + 4 <= iend; i += 4) {
+                const float4 h4 = *reinterpret_cast<const float4*>(ha + i);
+                a2 = fmaf(h4.x, ux[-i], a2);
+                a2 = fmaf(h4.y, ux[-i - 1], a2);
+                a2 = fmaf(h4.z, ux[-i - 2], a2);
+                a2 = fmaf(h4.w, ux[-i - 3], a2);
+            }
+            for (; i < iend; ++i) a2 = fmaf(ha[i], ux[-i], a2);
             cor[jp] = a2;
         }
     }
-    __syncthreads();
+    team_sync(TS);
     // ---- stage 5: add the corner, stage through shared memory for coalesced float4 stores ---------
     float* outs = u;                                    // window no longer needed
     if (live) {
@@ -476,12 +528,12 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
             if (j >= jw) acc[r] += cor[j - jw];
         }
     }
-    __syncthreads();
+    team_sync(TS);
     if (live) {
 #pragma unroll
         for (int r = 0; r < 16; r += 4) *reinterpret_cast<float4*>(outs + 16 * l + r) = make_float4(acc[r], acc[r + 1], acc[r + 2], acc[r + 3]);
     }
-    __syncthreads();
+    team_sync(TS);
     if (live) {
         float* yp = y + frame * hop;
         for (int q = l; q < (hop >> 2); q += TS) {
@@ -566,7 +618,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
 
     for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
     for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
-    __syncthreads();
+    team_sync(TS);
     if (live) {
         const float* gf = g + frame * hop;
         const float* nf = noise ? noise + frame * hop : nullptr;
@@ -583,7 +635,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
         }
         for (int i = l; i < L.n_g2; i += TS) g2[i] = i < half ? gf[jw + i] : 0.f;
     }
-    __syncthreads();
+    team_sync(TS);
     if (live) {
         // ---- d hc[q] = sum_j g[j] u[j-q] ----------------------------------------------------------
         const int SL = hop / nsl;
@@ -608,14 +660,22 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
             for (int d = 0; d < 8; ++d) part[(q0 + d) * nsl + sl] = acc[d];
         }
         // ---- d ha[i] = sum_{j'} g[hop-M/2+j'] u[j'-i] ---------------------------------------------
+        // u[jp - i] = 0 for jp < i: start at the pass's first i (team-uniform, multiple of 4 when TS is)
         for (int i = l; i < half; i += TS) {
             float a2 = 0.f;
             const float* ux = uc + half - i;
-            for (int jp = 0; jp < half; ++jp) a2 = fmaf(g2[jp], ux[jp], a2);
+            const int j0 = (i - l) & ~3;
+            for (int jp = j0; jp < half; jp += 4) {
+                const float4 g4 = *reinterpret_cast<const float4*>(g2 + jp);
+                a2 = fmaf(g4.x, ux[jp], a2);
+                a2 = fmaf(g4.y, ux[jp + 1], a2);
+                a2 = fmaf(g4.z, ux[jp + 2], a2);
+                a2 = fmaf(g4.w, ux[jp + 3], a2);
+            }
             dha[i] = a2;
         }
     }
-    __syncthreads();
+    team_sync(TS);
     if (live) {
         // ---- d r[p] = hann[M/2+p] * (d hc[p] + d ha[M/2-p]) ---------------------------------------
         const float invh = 1.0f / (float)half;
@@ -627,27 +687,36 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
             dr[p] = v * (0.5f + 0.5f * cospif((float)p * invh));
         }
     }
-    __syncthreads();
+    team_sync(TS);
     if (live) {
         // ---- d H[m] = kappa_m/M sum_p d r[p] cos(2 pi m p/M); m and M/2-m share even/odd partial sums
         const int M = 2 * half;
         const float invM = 1.0f / (float)M;
-        for (int m = l; 2 * m <= half; m += TS) {
+        for (int m = l; 2 * m < half; m += TS) {
             const float sh = sinpif((float)m * invM);
             const float dl = -4.f * sh * sh;
             float e = -0.5f * dl, c = 1.f;
             float E = 0.f, O = 0.f;
-            int p = 0;
-            for (; p + 1 <= half; p += 2) {
-                E = fmaf(dr[p], c, E);
-                e = fmaf(dl, c, e); c += e;
-                O = fmaf(dr[p + 1], c, O);
-                e = fmaf(dl, c, e); c += e;
+            for (int p4 = 0; p4 <= half; p4 += 4) {
+                const float4 d4 = *reinterpret_cast<const float4*>(dr + p4);
+                const float dv[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int p = p4 + k;
+                    if (p > half) continue;
+                    if (p & 1) O = fmaf(dv[k], c, O); else E = fmaf(dv[k], c, E);
+                    e = fmaf(dl, c, e); c += e;
+                }
             }
-            if (p <= half) E = fmaf(dr[p], c, E);
             const int m2 = half - m;
             gH[frame * NB + m] = (E + O) * ((m == 0 || m == half) ? invM : 2.f * invM);
             gH[frame * NB + m2] = (E - O) * ((m2 == 0 || m2 == half) ? invM : 2.f * invM);
+        }
+        if ((half & 1) == 0 && l == (half / 2) % TS) {   // m = half/2: cos(p pi/2) = 0, +-1
+            float E = 0.f;
+            for (int p = 0; p <= half; p += 4) E += dr[p];
+            for (int p = 2; p <= half; p += 4) E -= dr[p];
+            gH[frame * NB + half / 2] = E * (2.f * invM);
         }
     }
 }
