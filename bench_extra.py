@@ -8,6 +8,7 @@ contract).  One JSON line per workload:
   reverb  cfg 1' shapes (B=16, N=88064, L=44100) and a large batch (B=256, N=192000, L=48000): fwd + bwd (gx, gir)
   path    cfg 1': oscillator + noise + reverb + 6-scale MSS, forward + backward through the module API
   ctrl    row X1: fused Controller tail vs the torch expression at cfg 2's shapes
+  rtdec   cfg 3 with the Controller in front (RealtimeSynth), eager vs CUDA-graph replay
   rt      cfg 3: OscillatorBank.live + FilteredNoise + Reverb.live_forward per 2048-sample block, p50/p99 latency
 No CPU fallback: needs the CUDA library and a GPU.
 """
@@ -155,6 +156,32 @@ def bench_rt(args, dev):
             "out_shape": list(out.shape)}
 
 
+def bench_rtdec(args, dev):
+    """cfg 3 end to end (row X4): features -> Controller (GRU) -> live synthesis -> pinned host samples through
+    RealtimeSynth, eager and as a CUDA-graph replay; host wall-clock per 2048-sample block."""
+    import ddsp_pytorch_b200 as d
+    from ddsp_pytorch_b200.realtime import RealtimeSynth
+    conf = d.SHIPPED
+    out = []
+    for graph in (False, True):
+        torch.manual_seed(0)
+        rt = RealtimeSynth(conf, dev, frames_per_block=4, noise_seed=7, graph=graph)
+        g = torch.Generator().manual_seed(1)
+        feats = [{"f0": (torch.rand(1, 4, 1, generator=g) * 400 + 100).pin_memory(),
+                  "normalized_cents": torch.rand(1, 4, 1, generator=g).pin_memory(),
+                  "loudness": torch.rand(1, 4, 1, generator=g).pin_memory()} for _ in range(16)]
+        for i in range(50):
+            rt.process(feats[i % 16])
+        rt.latencies_ms.clear()
+        rt.missed = 0
+        for i in range(args.rt_calls):
+            rt.process(feats[i % 16])
+        st = rt.stats()
+        out.append({"workload": f"cfg3 rt decoder block ({rt.block} samples @ {conf.sample_rate} Hz): controller + live synth + D2H, "
+                                f"graph={graph}", **st})
+    return out
+
+
 def bench_fft(args, dev):
     from ddsp_pytorch_b200 import _lib
     out = []
@@ -214,7 +241,7 @@ def main():
         raise RuntimeError("bench_extra.py needs a CUDA device; there is no CPU fallback")
     dev = torch.device("cuda", 0)
     torch.manual_seed(0)
-    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt, "ctrl": bench_ctrl}
+    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt, "ctrl": bench_ctrl, "rtdec": bench_rtdec}
     for w in args.workloads.split(","):
         res = table[w](args, dev)
         for r in (res if isinstance(res, list) else [res]):

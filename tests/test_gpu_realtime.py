@@ -34,7 +34,7 @@ def test_blocks_match_oracle_live_path_and_keep_state():
             ctrl, _ = dec.controller({k: v.cuda() for k, v in z.items()}, rt.hidden)
         c, a, Hh, f0 = (ctrl[k].detach().cpu().double() for k in ("c", "a", "H", "f0"))
         harm, last = O.oscillator_bank_live(f0, c, a, last, conf.n_harmonics, conf.sample_rate, conf.hop_length)
-        u = torch.from_numpy(noise_uniform(1, 4, conf.hop_length, 3, blk, 0)).double()
+        u = torch.from_numpy(noise_uniform(1, 4, conf.hop_length, 3, blk + 1, 0)).double()   # device call counter: 1, 2, ..
         dry = harm + O.filtered_noise(Hh, conf.hop_length, u)
         want, buf = O.reverb_live(buf, dry, ir)
         err = float((got - want.view(-1)).abs().max())
@@ -42,3 +42,28 @@ def test_blocks_match_oracle_live_path_and_keep_state():
         assert err <= 1e-4 * max(1.0, float(want.abs().max()))
     st = rt.stats()
     assert st["blocks"] == 5 and st["p50_ms"] > 0
+
+
+def test_graph_replay_continues_the_eager_stream():
+    """graph=True (blocks 0-1 eager, then CUDA-graph replays) produces the same audio as the all-eager pipeline."""
+    import test_train_gloo as H
+    from ddsp_pytorch_b200.realtime import RealtimeSynth
+    from ddsp_pytorch_b200.train import synthetic_batch
+    conf = H.small_conf()
+    conf.sample_rate, conf.hop_length, conf.n_noise_filters = 4000, 64, 9
+    outs = []
+    for graph in (False, True):
+        torch.manual_seed(1)
+        rt = RealtimeSynth(conf, "cuda:0", frames_per_block=4, noise_seed=3, graph=graph)
+        rt.decoder.reverb.wet.data.fill_(1.0)
+        blocks = []
+        for blk in range(7):
+            feats = synthetic_batch(conf, 1, "cpu", seed=10 + blk)
+            z = {k: v[:, :4].contiguous() for k, v in feats.items() if k != "audio"}
+            blocks.append(torch.from_numpy(rt.process(z).copy()))
+        outs.append(torch.stack(blocks))
+        assert (rt._g is not None) == graph
+    eager, graphed = outs
+    assert float(eager.abs().max()) > 1e-3
+    assert float((eager - graphed).abs().max()) <= 1e-6 * float(eager.abs().max())
+    assert not torch.equal(graphed[3], graphed[4])            # state and noise advance between replays
