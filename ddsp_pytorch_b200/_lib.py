@@ -32,7 +32,7 @@ SIGNATURES = {
     "ddsp_reverb_impulse_backward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "ddsp_conv_scratch_bytes": (_sz, [_i, _i, _i]),
     "ddsp_conv_forward": (_i, [_p, _p, _p, _p, _i, _i, _i, _p]),
-    "ddsp_conv_backward": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p]),
+    "ddsp_conv_backward": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "ddsp_reverb_live": (_i, [_p, _p, _p, _p, _p, _i, _i, _p]),
     "ddsp_mss_count": (C.c_int64, [_i, _i, _i, _i]),
     "ddsp_mss_forward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, C.c_float, C.c_float, _i, _i, _p]),

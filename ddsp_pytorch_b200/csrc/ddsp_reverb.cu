@@ -371,7 +371,7 @@ extern "C" int ddsp_conv_forward(const float* x, const float* ir, float* y, void
 }
 
 extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* ir, float* gx, float* gir, void* scratch, int B,
-                                  int N, int Lk, void* stream) {
+                                  int N, int Lk, int scratch_from_forward, void* stream) {
     if (check_conv("ddsp_conv_backward", B, N, Lk)) return 1;
     DDSP_REQUIRE(g && ir && scratch && (gx || gir) && (x || !gir), "ddsp_conv_backward: null pointer argument");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -384,21 +384,13 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
     float2* part = reinterpret_cast<float2*>(base + p.off_part);
     const size_t smem = sizeof(float2) * fft8_smem_elems(CONV_N2);
     const int Le = Lk < N ? Lk : N;
-    if (gx) {      // gx = flip(conv(flip(g), ir))
-        conv_spectra_kernel<<<dim3(p.np, 1), CONV_THREADS, smem, st>>>(ir, Hf, 1, Le, p.np, 1, 0, 1);
-        DDSP_CHECK_LAUNCH("conv_spectra_kernel(ir)");
-        conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S0, B, N, p.nblk, 3, 1, 0);
-        DDSP_CHECK_LAUNCH("conv_spectra_kernel(flip g)");
-        for (int jg = 0; jg < p.np; jg += MAC_NP) {
-            conv_mac_kernel<<<dim3(CONV_N2 / MAC_THREADS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
-            DDSP_CHECK_LAUNCH("conv_mac_kernel(gx)");
-        }
-        conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, gx, B, N, p.nblk, 1);
-        DDSP_CHECK_LAUNCH("conv_ifft_kernel(gx)");
-    }
+    // The kernel gradient goes first: with scratch_from_forward the block spectra of x (S0) and of the kernel (Hf) are
+    // still the ones ddsp_conv_forward left there; the gx pass below then overwrites S0.
     if (gir) {
-        conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(x, S0, B, N, p.nblk, 3, 0, 0);
-        DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
+        if (!scratch_from_forward) {
+            conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(x, S0, B, N, p.nblk, 3, 0, 0);
+            DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
+        }
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S1, B, N, p.nblk, 2, 0, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(g tail)");
         const int nchunks = p.B2 < GIR_CHUNKS ? p.B2 : GIR_CHUNKS;
@@ -410,6 +402,20 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         DDSP_REQUIRE(e == cudaSuccess, "ddsp_conv_backward: memset failed: %s", cudaGetErrorString(e));
         conv_gir_finish_kernel<<<p.np, CONV_THREADS, smem, st>>>(part, gir, p.np, Le, nchunks);
         DDSP_CHECK_LAUNCH("conv_gir_finish_kernel");
+    }
+    if (gx) {      // gx = flip(conv(flip(g), ir))
+        if (!scratch_from_forward) {
+            conv_spectra_kernel<<<dim3(p.np, 1), CONV_THREADS, smem, st>>>(ir, Hf, 1, Le, p.np, 1, 0, 1);
+            DDSP_CHECK_LAUNCH("conv_spectra_kernel(ir)");
+        }
+        conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S0, B, N, p.nblk, 3, 1, 0);
+        DDSP_CHECK_LAUNCH("conv_spectra_kernel(flip g)");
+        for (int jg = 0; jg < p.np; jg += MAC_NP) {
+            conv_mac_kernel<<<dim3(CONV_N2 / MAC_THREADS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+            DDSP_CHECK_LAUNCH("conv_mac_kernel(gx)");
+        }
+        conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, gx, B, N, p.nblk, 1);
+        DDSP_CHECK_LAUNCH("conv_ifft_kernel(gx)");
     }
     return 0;
 }

@@ -211,6 +211,8 @@ class _CausalConv(torch.autograd.Function):
             _lib.call("ddsp_conv_forward", x_.data_ptr(), ir_.data_ptr(), y.data_ptr(), scratch.data_ptr(), B, N, Lk, _stream())
         ctx.save_for_backward(x_, ir_)
         ctx.meta = (x.dtype, ir.shape, ir.dtype)
+        # the block spectra of x and ir stay in `scratch`; the first backward reuses them (and then overwrites them)
+        ctx.scratch = scratch if (x.requires_grad or ir.requires_grad) else None
         return y
 
     @staticmethod
@@ -223,10 +225,13 @@ class _CausalConv(torch.autograd.Function):
         gx = torch.empty(B, N, dtype=torch.float32, device=x_.device) if need_x else None
         gir = torch.empty(Lk, dtype=torch.float32, device=x_.device) if need_ir else None
         with torch.cuda.device(x_.device):
-            scratch = _bytes(_lib.load().ddsp_conv_scratch_bytes(B, N, Lk), x_.device)
+            scratch, reuse = getattr(ctx, "scratch", None), 1
+            ctx.scratch = None
+            if scratch is None:
+                scratch, reuse = _bytes(_lib.load().ddsp_conv_scratch_bytes(B, N, Lk), x_.device), 0
             _lib.call("ddsp_conv_backward", g_.data_ptr(), x_.data_ptr(), ir_.data_ptr(),
                       gx.data_ptr() if need_x else None, gir.data_ptr() if need_ir else None, scratch.data_ptr(), B, N, Lk,
-                      _stream())
+                      reuse, _stream())
         xd, irs, ird = ctx.meta
         return (gx.to(xd) if need_x else None), (gir.view(irs).to(ird) if need_ir else None)
 

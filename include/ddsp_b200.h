@@ -125,9 +125,12 @@ int ddsp_reverb_impulse_backward(const float* gir, const float* noise, const flo
 size_t ddsp_conv_scratch_bytes(int B, int N, int Lk);
 int ddsp_conv_forward(const float* x, const float* ir, float* y, void* scratch, int B, int N, int Lk,
                       void* stream);
-/* gx[b,m] = sum_{n>=m} g[b,n]*ir[n-m];  gir[q] = sum_b sum_{n>=q} g[b,n]*x[b,n-q]. Either output may be NULL. */
+/* gx[b,m] = sum_{n>=m} g[b,n]*ir[n-m];  gir[q] = sum_b sum_{n>=q} g[b,n]*x[b,n-q]. Either output may be NULL.
+ * scratch_from_forward != 0: `scratch` is the buffer the matching ddsp_conv_forward call (same x, ir, B, N, Lk)
+ * used and nothing has written to it since -- the block spectra of x and ir in it are reused instead of being
+ * recomputed.  The call overwrites them, so a second backward on the same buffer must pass 0. */
 int ddsp_conv_backward(const float* g, const float* x, const float* ir, float* gx, float* gir,
-                       void* scratch, int B, int N, int Lk, void* stream);
+                       void* scratch, int B, int N, int Lk, int scratch_from_forward, void* stream);
 
 /* Reverb.live_forward, reverb.py:40-49: buffer[L] <- shift left by n, append x[n]; y[n] = last n
  * samples of causal_conv(buffer, ir). */

@@ -60,6 +60,24 @@ def test_conv_against_oracle(B, N, L):
     assert rel(irc.grad, ird.grad) <= TOL
 
 
+def test_conv_backward_twice_and_partial_grads():
+    """The first backward reuses the spectra the forward left in its scratch buffer and overwrites them; a second
+    backward (retain_graph) recomputes them -- both give the same bits.  Also gradient w.r.t. only one of the inputs."""
+    from ddsp_pytorch_b200 import ops
+    gen = torch.Generator().manual_seed(5)
+    x = (torch.randn(3, 9000, generator=gen) * 0.3).cuda().requires_grad_(True)
+    ir = (torch.randn(1, 5000, generator=gen) * torch.exp(-torch.arange(5000) / 1000.0)).cuda().requires_grad_(True)
+    gup = torch.randn(3, 9000, generator=gen).cuda()
+    y = ops.causal_conv(x, ir)
+    g1 = torch.autograd.grad((y * gup).sum(), (x, ir), retain_graph=True)
+    g2 = torch.autograd.grad((y * gup).sum(), (x, ir))
+    assert torch.equal(g1[0], g2[0]) and torch.equal(g1[1], g2[1])
+    y = ops.causal_conv(x.detach(), ir)                 # kernel gradient only
+    assert torch.equal(torch.autograd.grad((y * gup).sum(), ir)[0], g1[1])
+    y = ops.causal_conv(x, ir.detach())                 # signal gradient only
+    assert torch.equal(torch.autograd.grad((y * gup).sum(), x)[0], g1[0])
+
+
 def test_reverb_module_forward_and_live(golden):
     import ddsp_pytorch_b200 as d
     g = golden("ref_reverb_live.npz")
