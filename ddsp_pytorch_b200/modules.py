@@ -68,10 +68,15 @@ OscillatorBank.live = _live
 
 
 def fft_convolve(signal: torch.Tensor, kernel: torch.Tensor) -> torch.Tensor:
-    """filtered_noise.py:25-32 for the shapes the reference uses it with a shared kernel: signal [B,n], kernel [1,n]."""
-    if signal.dim() != 2 or kernel.numel() != kernel.shape[-1]:
-        raise RuntimeError("fft_convolve: this build supports signal [B,n] with one shared kernel [1,n]")
-    return ops.causal_conv(signal, kernel)
+    """filtered_noise.py:25-32: causal convolution along the last axis, truncated to its length n.  A single kernel
+    shared by a [B,n] signal (how Reverb.forward calls it) goes through the partitioned FFT convolution; any other
+    broadcastable pair of shapes (how FilteredNoise calls it: [B,T,n] x [B,T,n]) through the per-row kernel."""
+    if signal.shape[-1] != kernel.shape[-1]:
+        raise RuntimeError(f"fft_convolve: last dimensions differ ({signal.shape[-1]} vs {kernel.shape[-1]})")
+    if signal.dim() == 2 and kernel.numel() == kernel.shape[-1]:
+        return ops.causal_conv(signal, kernel)
+    shape = torch.broadcast_shapes(signal.shape, kernel.shape)
+    return ops.row_conv(signal.expand(shape).contiguous(), kernel.expand(shape).contiguous())
 
 
 amp_to_impulse_response = ops.amp_to_impulse_response

@@ -243,6 +243,43 @@ def causal_conv(x: torch.Tensor, ir: torch.Tensor) -> torch.Tensor:
     return _CausalConv.apply(x, ir)
 
 
+class _RowConv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, signal, kernel):
+        s_, k_ = _f32(signal), _f32(kernel)
+        n = s_.shape[-1]
+        rows = s_.numel() // n
+        y = torch.empty_like(s_)
+        with torch.cuda.device(s_.device):
+            _lib.call("ddsp_rowconv_forward", s_.data_ptr(), k_.data_ptr(), y.data_ptr(), rows, n, _stream())
+        ctx.save_for_backward(s_, k_)
+        ctx.meta = (signal.dtype, kernel.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        s_, k_ = ctx.saved_tensors
+        n = s_.shape[-1]
+        rows = s_.numel() // n
+        g_ = _f32(g)
+        need_s, need_k = ctx.needs_input_grad
+        gs = torch.empty_like(s_) if need_s else None
+        gk = torch.empty_like(k_) if need_k else None
+        with torch.cuda.device(s_.device):
+            _lib.call("ddsp_rowconv_backward", g_.data_ptr(), s_.data_ptr(), k_.data_ptr(), gs.data_ptr() if need_s else None,
+                      gk.data_ptr() if need_k else None, rows, n, _stream())
+        sd, kd = ctx.meta
+        return (gs.to(sd) if need_s else None), (gk.to(kd) if need_k else None)
+
+
+def row_conv(signal: torch.Tensor, kernel: torch.Tensor) -> torch.Tensor:
+    """signal [...,n], kernel of the SAME shape -> y[..., m] = sum_{q<=m} kernel[..., q] * signal[..., m-q]
+    (fft_convolve with one kernel per row, filtered_noise.py:25-32); n <= 4096."""
+    if signal.shape != kernel.shape:
+        raise RuntimeError(f"row_conv: signal {tuple(signal.shape)} and kernel {tuple(kernel.shape)} must have the same shape")
+    return _RowConv.apply(signal, kernel)
+
+
 def reverb_live(buffer: torch.Tensor, x: torch.Tensor, ir: torch.Tensor) -> torch.Tensor:
     """Reverb.live_forward (reverb.py:40-49): updates ``buffer`` [1,L] in place, returns the last len(x) outputs [1,n]."""
     x_, ir_ = _f32(x).view(-1), _f32(ir).view(-1)

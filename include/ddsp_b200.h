@@ -132,6 +132,15 @@ int ddsp_conv_forward(const float* x, const float* ir, float* y, void* scratch, 
 int ddsp_conv_backward(const float* g, const float* x, const float* ir, float* gx, float* gir,
                        void* scratch, int B, int N, int Lk, int scratch_from_forward, void* stream);
 
+/* fft_convolve with one kernel per row, filtered_noise.py:25-32 in its general call shape (signal [...,n],
+ * kernel [...,n], flattened to `rows` rows): y[r,m] = sum_{q<=m} kernel[r,q] * signal[r,m-q].  n <= 4096.
+ * backward: gsignal[r,j] = sum_{m>=j} g[r,m]*kernel[r,m-j], gkernel[r,q] = sum_{m>=q} g[r,m]*signal[r,m-q];
+ * either output may be NULL. */
+int ddsp_rowconv_forward(const float* signal, const float* kernel, float* y, long long rows, int n,
+                         void* stream);
+int ddsp_rowconv_backward(const float* g, const float* signal, const float* kernel, float* gsignal,
+                          float* gkernel, long long rows, int n, void* stream);
+
 /* Reverb.live_forward, reverb.py:40-49: buffer[L] <- shift left by n, append x[n]; y[n] = last n
  * samples of causal_conv(buffer, ir). */
 int ddsp_reverb_live(float* buffer, const float* x, const float* ir, float* y, void* scratch, int L,

@@ -87,3 +87,37 @@ def test_module_draws_fresh_noise_each_call():
     H = torch.rand(2, 3, 65).cuda()
     a, b = mod({"H": H}), mod({"H": H})
     assert a.shape == (2, 3 * 512) and not torch.equal(a, b)
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 64), (5, 100), (1, 4096), (3, 1), (2, 2, 7), (4, 5, 512)])
+def test_fft_convolve_per_row_kernels(shape):
+    """modules.fft_convolve in the call shape FilteredNoise uses in the reference ([B,T,n] x [B,T,n],
+    filtered_noise.py:50): per-row causal convolution and both adjoints against the oracle in fp64."""
+    from ddsp_pytorch_b200 import modules
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(sum(shape))
+    s = torch.randn(*shape, generator=gen)
+    k = torch.randn(*shape, generator=gen) * 0.3
+    gup = torch.randn(*shape, generator=gen)
+    sd, kd = s.double().requires_grad_(True), k.double().requires_grad_(True)
+    want = O.causal_conv(sd, kd)
+    (want * gup.double()).sum().backward()
+    sc, kc = s.cuda().requires_grad_(True), k.cuda().requires_grad_(True)
+    got = modules.fft_convolve(sc, kc)
+    (got * gup.cuda()).sum().backward()
+    scale = float(want.abs().max()) + 1e-12
+    assert got.shape == want.shape
+    assert float((got.double().cpu() - want.detach()).abs().max()) <= 1e-5 * scale
+    assert float((sc.grad.double().cpu() - sd.grad).abs().max()) <= 1e-5 * float(sd.grad.abs().max() + 1e-12)
+    assert float((kc.grad.double().cpu() - kd.grad).abs().max()) <= 1e-5 * float(kd.grad.abs().max() + 1e-12)
+
+
+def test_fft_convolve_broadcast_kernel():
+    """A [T,n] kernel shared over the batch broadcasts like the reference's elementwise product of spectra."""
+    from ddsp_pytorch_b200 import modules
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(3)
+    s, k = torch.randn(3, 4, 32, generator=gen), torch.randn(4, 32, generator=gen)
+    want = O.causal_conv(s.double(), k.double())
+    got = modules.fft_convolve(s.cuda(), k.cuda())
+    assert float((got.double().cpu() - want).abs().max()) <= 1e-5 * float(want.abs().max())
