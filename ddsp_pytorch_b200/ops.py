@@ -341,12 +341,27 @@ class _MSSLoss(torch.autograd.Function):
         return out.to(dt), None, None, None, None, None, None
 
 
+_HANN_CACHE = {}
+
+
+def _torch_hann(n: int, device) -> torch.Tensor:
+    """torch.hann_window's own fp32 values (what torchaudio's Spectrogram holds, mss_loss.py:23).  The kernel's built-in
+    Hann is rounded from fp64 and differs from these by an ulp in places -- enough to move the near-empty bins that
+    dominate d log2(S + eps)/dx by 1e-4, so the default is the reference's table, not the kernel's."""
+    key = (int(n), str(device))
+    if key not in _HANN_CACHE:
+        _HANN_CACHE[key] = torch.hann_window(int(n), dtype=torch.float32).to(device)
+    return _HANN_CACHE[key]
+
+
 def mss_loss(x_pred, x_true, n_ffts, alpha: float = 1.0, overlap: float = 0.75, eps: float = 1e-7, windows=None) -> torch.Tensor:
     """MSSLoss.forward (mss_loss.py:57-68) on tensors [B,N] -> 0-dim fp32 loss; gradient flows to x_pred only.
-    ``windows``: optional per-scale fp32 analysis windows (the modules pass their ``stft.window`` buffers)."""
+    ``windows``: optional per-scale fp32 analysis windows (the modules pass their ``stft.window`` buffers); default:
+    torch.hann_window(n) as the reference's Spectrogram builds it."""
     hops = [int(n * (1 - overlap)) for n in n_ffts]          # mss_loss.py:21
-    return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps),
-                          None if windows is None else tuple(windows))
+    if windows is None:
+        windows = [_torch_hann(n, x_pred.device) for n in n_ffts]
+    return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps), tuple(windows))
 
 
 def oscillator_live(f0, c, a, last_phases, sample_rate: int, hop: int):

@@ -161,7 +161,9 @@ int64_t ddsp_mss_count(int B, int N, int n_fft, int hop);
  *   gx [B,N] or NULL (zeroed here): d loss / d x_pred, produced in the same pass.
  *   n_ffts_host / hops_host: HOST int arrays; n_fft a power of two in [4,4096], n_fft/2 < N;
  *   windows_host: NULL, or a HOST array of n_scales device pointers (entries may be NULL) to the fp32 analysis
- *     windows [n_fft] -- the reference's `stft.window` buffers (mss_loss.py:23); NULL = periodic Hann. */
+ *     windows [n_fft] -- the reference's `stft.window` buffers (mss_loss.py:23); NULL = periodic Hann rounded
+ *     from fp64, which differs from torch.hann_window's fp32 table by an ulp in places: pass the table when the
+ *     gradient has to match the reference bin for bin on near-silent input. */
 int ddsp_mss_forward(const float* x_pred, const float* x_true, double* loss_terms, float* loss_f32,
                      float* gx, const int* n_ffts_host, const int* hops_host,
                      const float* const* windows_host, int n_scales, float alpha, float eps, int B, int N,
