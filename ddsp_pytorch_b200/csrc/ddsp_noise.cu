@@ -87,6 +87,7 @@ __device__ __forceinline__ void load_noise(const NoiseSmem& s, const float* __re
     const int tid = threadIdx.x, nt = blockDim.x;
     for (int i = tid; i < s.PADL; i += nt) s.u[i] = 0.f;
     float* u = s.u + s.PADL;
+    for (int i = hop + tid; i < ((hop + 7) & ~7); i += nt) u[i] = 0.f;        // tail of the last 8-sample group (hop % 8 != 0)
     if (noise_frame) {
         for (int i = tid; i < hop; i += nt) u[i] = noise_frame[i];
     } else {
@@ -106,7 +107,7 @@ __device__ __forceinline__ void load_noise(const NoiseSmem& s, const float* __re
 }
 
 // ------------------------------------------------------------------------------------------------
-// forward: grid (T, B), hop/8 threads (hop % 8 == 0), thread owns outputs j0..j0+7
+// forward: grid (T, B), ceil(hop/8) threads, thread owns outputs j0..j0+7 (masked past hop)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512) noise_fwd_kernel(const float* __restrict__ H, const float* __restrict__ noise,
                                                         float* __restrict__ y, int accumulate, uint2 key, uint32_t offset,
@@ -114,7 +115,7 @@ __global__ void __launch_bounds__(512) noise_fwd_kernel(const float* __restrict_
                                                         int NB, int hop) {
     extern __shared__ __align__(16) float smem[];
     if (offset_dev) offset += *offset_dev;
-    const NoiseSmem s = carve_noise_smem(smem, NB, hop);
+    const NoiseSmem s = carve_noise_smem(smem, NB, (hop + 7) & ~7);     // any hop: the last thread's group is partly masked
     const int t = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const size_t frame = (size_t)b * T + t;
     for (int m = tid; m < NB; m += blockDim.x) s.Hs[m] = H[frame * NB + m];
@@ -156,21 +157,27 @@ __global__ void __launch_bounds__(512) noise_fwd_kernel(const float* __restrict_
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const int jp = j0 + r - jw;
-        if (jp >= 0) {
+        if (jp >= 0 && j0 + r < hop) {
             float a2 = 0.f;
             for (int i = 0; i <= jp; ++i) a2 = fmaf(s.ha[i], u[jp - i], a2);
             acc[r] += a2;
         }
     }
     float* yp = y + frame * hop + j0;
-    float4 o0 = make_float4(acc[0], acc[1], acc[2], acc[3]), o1 = make_float4(acc[4], acc[5], acc[6], acc[7]);
-    if (accumulate) {
-        const float4 p0 = *reinterpret_cast<const float4*>(yp), p1 = *reinterpret_cast<const float4*>(yp + 4);
-        o0.x += p0.x; o0.y += p0.y; o0.z += p0.z; o0.w += p0.w;
-        o1.x += p1.x; o1.y += p1.y; o1.z += p1.z; o1.w += p1.w;
+    if ((hop & 3) == 0 && j0 + 8 <= hop) {
+        float4 o0 = make_float4(acc[0], acc[1], acc[2], acc[3]), o1 = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        if (accumulate) {
+            const float4 p0 = *reinterpret_cast<const float4*>(yp), p1 = *reinterpret_cast<const float4*>(yp + 4);
+            o0.x += p0.x; o0.y += p0.y; o0.z += p0.z; o0.w += p0.w;
+            o1.x += p1.x; o1.y += p1.y; o1.z += p1.z; o1.w += p1.w;
+        }
+        *reinterpret_cast<float4*>(yp) = o0;
+        *reinterpret_cast<float4*>(yp + 4) = o1;
+    } else {                                            // rows not 16-byte aligned, or the masked tail group
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+            if (j0 + r < hop) yp[r] = accumulate ? yp[r] + acc[r] : acc[r];
     }
-    *reinterpret_cast<float4*>(yp) = o0;
-    *reinterpret_cast<float4*>(yp + 4) = o1;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -199,14 +206,15 @@ __global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict_
     extern __shared__ __align__(16) float smem[];
     if (offset_dev) offset += *offset_dev;
     const int M = 2 * (NB - 1), half = NB - 1, TP = noise_tp(NB), PADL = TP + 8;
+    const int hopp = (hop + 7) & ~7;                   // sample loops run in groups of 8; g and u are zero past hop
     float* ct = smem;
     float* dr = ct + ((M + 3) & ~3);
-    float* gs = dr + ((half + 1 + 3) & ~3);            // [hop]    upstream gradient of this frame
-    float* g2 = gs + hop;                              // [TP+8]   gradient seen by the wrapped taps, zero padded
+    float* gs = dr + ((half + 1 + 3) & ~3);            // [hopp]   upstream gradient of this frame
+    float* g2 = gs + hopp;                             // [TP+8]   gradient seen by the wrapped taps, zero padded
     NoiseSmem s;
     s.TP = TP; s.PADL = PADL;
-    s.u = g2 + TP + 8;                                 // [PADL+hop]
-    float* dpc = s.u + PADL + hop;                     // [TP][nsl] partial d hc
+    s.u = g2 + TP + 8;                                 // [PADL+hopp]
+    float* dpc = s.u + PADL + hopp;                    // [TP][nsl] partial d hc
     float* dpa = dpc + (size_t)TP * nsl;               // [TP][nsl] partial d ha
     const int t = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
     const size_t frame = (size_t)b * T + t;
@@ -214,14 +222,14 @@ __global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict_
     const float invM = 1.0f / (float)M;
 
     for (int i = tid; i < M; i += nt) ct[i] = cospif(2.0f * (float)i * invM);
-    for (int i = tid; i < hop; i += nt) gs[i] = g[frame * hop + i];
+    for (int i = tid; i < hopp; i += nt) gs[i] = i < hop ? g[frame * hop + i] : 0.f;
     for (int i = tid; i < TP + 8; i += nt) g2[i] = (i < half) ? g[frame * hop + jw + i] : 0.f;
     load_noise(s, noise ? noise + frame * hop : nullptr, hop, (uint32_t)t, voice_offset + (uint32_t)b, offset, key);
     __syncthreads();
 
     const float* u = s.u + PADL;
     const int qg = tid / nsl, sl = tid % nsl;
-    const int q0 = 8 * qg, SL = hop / nsl;
+    const int q0 = 8 * qg, SL = hopp / nsl;
     float acc[8], acc2[8];
 #pragma unroll
     for (int d = 0; d < 8; ++d) acc[d] = acc2[d] = 0.f;
@@ -762,7 +770,7 @@ static int check_noise_shape(const char* fn, int B, int T, int NB, int hop) {
     DDSP_REQUIRE(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
     DDSP_REQUIRE(T >= 1, "%s: T=%d must be >= 1", fn, T);
     DDSP_REQUIRE(NB >= 2, "%s: NB=%d must be >= 2", fn, NB);
-    DDSP_REQUIRE(hop >= 8 && hop % 8 == 0 && hop <= 4096, "%s: hop=%d must be a multiple of 8 in [8,4096]", fn, hop);
+    DDSP_REQUIRE(hop >= 2 && hop <= 4096, "%s: hop=%d out of range [2,4096]", fn, hop);
     DDSP_REQUIRE(2 * (NB - 1) <= hop, "%s: FIR length 2(NB-1)=%d exceeds hop=%d (filtered_noise.py:19 pads by hop-M)", fn,
                  2 * (NB - 1), hop);
     return 0;
@@ -809,9 +817,10 @@ extern "C" int ddsp_noise_forward(const float* H, const float* noise, float* y, 
             return 0;
         }
     }
-    const size_t smem = sizeof(float) * noise_smem_floats(NB, hop);
+    const int hopp = (hop + 7) & ~7;
+    const size_t smem = sizeof(float) * noise_smem_floats(NB, hopp);
     if (reserve_smem(noise_fwd_kernel, smem, "noise_fwd_kernel")) return 1;
-    noise_fwd_kernel<<<dim3(T, B), hop / 8, smem, static_cast<cudaStream_t>(stream)>>>(H, noise, y, accumulate, key, offset,
+    noise_fwd_kernel<<<dim3(T, B), hopp / 8, smem, static_cast<cudaStream_t>(stream)>>>(H, noise, y, accumulate, key, offset,
                                                                                       offset_dev, voice_offset, T, NB, hop);
     DDSP_CHECK_LAUNCH("noise_fwd_kernel");
     return 0;
@@ -844,10 +853,11 @@ extern "C" int ddsp_noise_backward(const float* g, const float* noise, float* gH
             return 0;
         }
     }
-    const int nsl = noise_bwd_slices(NB, hop);
+    const int hopp = (hop + 7) & ~7;
+    const int nsl = noise_bwd_slices(NB, hopp);
     const int threads = noise_tp(NB) / 8 * nsl;
     DDSP_REQUIRE(threads <= 512, "ddsp_noise_backward: NB=%d needs %d threads per frame (max 512)", NB, threads);
-    const size_t smem = sizeof(float) * noise_bwd_smem_floats(NB, hop);
+    const size_t smem = sizeof(float) * noise_bwd_smem_floats(NB, hopp);
     if (reserve_smem(noise_bwd_kernel, smem, "noise_bwd_kernel")) return 1;
     noise_bwd_kernel<<<dim3(T, B), threads, smem, static_cast<cudaStream_t>(stream)>>>(g, noise, gH, key, offset, offset_dev,
                                                                                       voice_offset, T, NB, hop, nsl);

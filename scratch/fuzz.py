@@ -19,7 +19,8 @@ def check(name, cfg, pairs, tol):
     finite = all(torch.isfinite(a).all() == torch.isfinite(b).all() for a, b in pairs)
     if not (worst <= tol) and finite:
         bad += 1
-        print("FAIL", name, cfg, [f"{rel(a, b):.2e}" for a, b in pairs])
+        print("FAIL", name, cfg, [f"{rel(a, b):.2e}" for a, b in pairs], "max|ref|", [f"{float(b.abs().max()):.2e}" for a, b in pairs],
+              "max|diff|", [f"{float((a.double().cpu() - b.double().cpu()).abs().max()):.2e}" for a, b in pairs])
 
 for it in range(n_cases):
     try:
@@ -39,10 +40,10 @@ for it in range(n_cases):
         got = ops.oscillator_bank(f0.cuda(), cc, ac, sr, hop)
         (got * g.cuda()).sum().backward()
         ok = torch.isfinite(want).all()
-        if ok:
+        if ok and K > 1:        # K = 1: c/sum(c) == 1, the gradient is exactly zero
             check("osc", (B, T, K, hop, sr), [(got, want.detach()), (cc.grad, cd.grad), (ac.grad, ad.grad)], 2e-4)
         # noise
-        hopn = rnd.choice([16, 32, 64, 80, 128, 256, 512, 40, 100])
+        hopn = rnd.choice([16, 32, 64, 80, 128, 256, 512, 40, 100, 441, 7, 30, 250])
         NB = rnd.choice([2, 3, 5, 9, 17, 33, 65, 129, 195])
         if 2 * (NB - 1) > hopn:
             NB = hopn // 2 + 1

@@ -30,7 +30,9 @@ def test_golden_with_injected_noise(golden, name):
 
 
 @pytest.mark.parametrize("B,T,NB,hop", [(2, 5, 65, 512), (1, 3, 195, 512), (2, 2, 33, 64), (1, 4, 65, 128), (1, 2, 129, 256),
-                                        (1, 2, 5, 8), (2, 3, 2, 16)])
+                                        (1, 2, 5, 8), (2, 3, 2, 16),
+                                        # hops that are not a multiple of 8 / 4 / 2 (masked tail group, unaligned rows)
+                                        (2, 3, 17, 100), (1, 4, 101, 441), (3, 2, 3, 5), (1, 1, 2, 2), (2, 2, 4, 7), (1, 3, 9, 20)])
 def test_against_oracle(B, T, NB, hop):
     from ddsp_pytorch_b200 import ops
     from oracle import ddsp_oracle as O
