@@ -19,6 +19,13 @@
 
 namespace ddsp {
 
+// Segment s interpolates frames s-1 and s and holds the samples whose half-pixel position (n + 1/2)/hop - 1/2 lies in
+// [s-1, s): n0 = s hop - ceil(hop/2) is its first sample and sample r sits at fraction w = (r + phi)/hop between the two
+// frames, phi = 1/2 for even hops, 0 for odd hops (a sample then falls exactly on every frame centre).
+__host__ __device__ inline int half_up(int hop) { return (hop + 1) >> 1; }
+__host__ __device__ inline float seg_phi(int hop) { return (hop & 1) ? 0.f : 0.5f; }
+
+
 // ------------------------------------------------------------------------------------------------
 // frame-rate preparation: one CTA per voice
 // ------------------------------------------------------------------------------------------------
@@ -69,11 +76,12 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
     }
 
     // ---- phase prefix over segments, fp64, in cycles -------------------------------------------
-    // E_0 = -(hop/2) u_0 ; E_{s+1} = E_s + hop*(u_{max(s-1,0)} + u_s)/2          (u = f0 / sample_rate)
+    // hu = ceil(hop/2) samples of segment 0 lie before n = 0:  E_0 = -hu u_0.  Summing u over a whole segment,
+    // E_{s+1} = E_s + hu u_L + (hop - hu) u_R   (= hop (u_L + u_R)/2 for even hop)         (u = f0 / sample_rate)
     double* Eb = phase0 + (size_t)b * (T + 1);
     const double inv_sr = 1.0 / (double)sample_rate;
     if (tid == 0) {
-        const double e0 = -0.5 * hop * ((double)f0b[0] * inv_sr);
+        const double e0 = -(double)half_up(hop) * ((double)f0b[0] * inv_sr);
         carry_s = e0;
         Eb[0] = e0 - floor(e0);
     }
@@ -84,7 +92,7 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
         if (s < T) {
             const double uL = (double)f0b[s > 0 ? s - 1 : 0] * inv_sr;
             const double uR = (double)f0b[s] * inv_sr;
-            v = 0.5 * hop * (uL + uR);
+            v = (double)half_up(hop) * uL + (double)(hop - half_up(hop)) * uR;
         }
         // inclusive scan inside the warp, then across warps
 #pragma unroll
@@ -110,16 +118,16 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
         SegFix* sb = seg + (size_t)b * (T + 1);
         const double two64 = 18446744073709551616.0;
         auto ufix = [&](int t) { return (unsigned long long)__double2ll_rn((double)f0b[t] * inv_sr * two64); };
-        const unsigned long long hh = (unsigned long long)(hop / 2);
-        if (tid == 0) carry_u = 0ull - hh * ufix(0);
+        const unsigned long long hhL = (unsigned long long)half_up(hop), hhR = (unsigned long long)(hop - half_up(hop));
+        if (tid == 0) carry_u = 0ull - hhL * ufix(0);
         __syncthreads();
         for (int base = 0; base <= T; base += PREP_THREADS) {
-            const int s = base + tid;                      // segment index, E_s = E_0 + sum_{s'<s} (hop/2)(uL+uR)
+            const int s = base + tid;                      // segment index, E_s = E_0 + sum_{s'<s} (hu uL + (hop-hu) uR)
             unsigned long long uL = 0, uR = 0, v = 0;
             if (s <= T) {
                 uL = ufix(s > 0 ? s - 1 : 0);
                 uR = ufix(s < T ? s : T - 1);
-                v = hh * (uL + uR);
+                v = hhL * uL + hhR * uR;
             }
             unsigned long long inc = v;
 #pragma unroll
@@ -134,8 +142,10 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
             if (s <= T) {
                 SegFix g;
                 g.E = pre + inc - v;                       // exclusive prefix
-                g.uL = uL;
                 g.du = (long long)(uR - uL) / (2ll * hop);
+                // Theta(r) = E + (r+1) uL + du (r+1)(r + 2 phi): phi = 1/2 (even hop) gives du (r+1)^2; phi = 0 (odd hop)
+                // gives du (r+1)^2 - du (r+1), folded into the linear coefficient
+                g.uL = (hop & 1) ? uL - (unsigned long long)g.du : uL;
                 sb[s] = g;
             }
             __syncthreads();
@@ -158,12 +168,13 @@ __device__ __forceinline__ Segment make_segment(int s, int T, int hop, const flo
     Segment g;
     g.tL = s > 0 ? s - 1 : 0;
     g.tR = s < T ? s : T - 1;
-    g.r_lo = s == 0 ? hop / 2 : 0;
-    g.r_hi = s == T ? hop / 2 : hop;
-    g.n0 = (long long)s * hop - hop / 2;
+    g.r_lo = s == 0 ? half_up(hop) : 0;
+    g.r_hi = s == T ? half_up(hop) : hop;
+    g.n0 = (long long)s * hop - half_up(hop);
     g.E = Eb[s];
     g.uL = (double)f0b[g.tL] * inv_sr;
     g.du = ((double)f0b[g.tR] * inv_sr - g.uL) / (2.0 * hop);
+    if (hop & 1) g.uL -= g.du;                         // odd hop: see osc_prepare_kernel
     return g;
 }
 
@@ -206,9 +217,9 @@ __device__ __forceinline__ SegGeom seg_geom(int s, int T, int hop) {
     SegGeom g;
     g.tL = s > 0 ? s - 1 : 0;
     g.tR = s < T ? s : T - 1;
-    g.r_lo = s == 0 ? hop / 2 : 0;
-    g.r_hi = s == T ? hop / 2 : hop;
-    g.n0 = (long long)s * hop - hop / 2;
+    g.r_lo = s == 0 ? half_up(hop) : 0;
+    g.r_hi = s == T ? half_up(hop) : hop;
+    g.n0 = (long long)s * hop - half_up(hop);
     return g;
 }
 
@@ -274,13 +285,13 @@ __global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_synth_kernel(
     }
 
     const float aL = a[fL], da = a[fR] - aL;
-    const float inv_hop = 1.0f / (float)hop;
+    const float inv_hop = 1.0f / (float)hop, phi = seg_phi(hop);
     float out[R], zs[R];
 #pragma unroll
     for (int j = 0; j < RP; ++j) {
         const float2 zP = __ffma2_rn(sg[j], Po[j], Pe[j]);     // sin(m theta) = sigma^m sin(m theta')
         const float2 zQ = __ffma2_rn(sg[j], Qo[j], Qe[j]);
-        const float w0 = ((float)(r0 + 2 * j) + 0.5f) * inv_hop, w1 = ((float)(r0 + 2 * j + 1) + 0.5f) * inv_hop;
+        const float w0 = ((float)(r0 + 2 * j) + phi) * inv_hop, w1 = ((float)(r0 + 2 * j + 1) + phi) * inv_hop;
         zs[2 * j] = fmaf(w0, zQ.x, zP.x);
         zs[2 * j + 1] = fmaf(w1, zQ.y, zP.y);
         out[2 * j] = fmaf(w0, da, aL) * zs[2 * j];
@@ -364,7 +375,7 @@ __global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_grad_kernel(
         float u1[R], u2[R];
 #pragma unroll
         for (int j = 0; j < R; ++j) {
-            const float w = ((float)(r0 + j) + 0.5f) * inv_hop;
+            const float w = ((float)(r0 + j) + seg_phi(hop)) * inv_hop;
             const float gz = gj[j] * zj[j];
             ga0 += gz;
             ga1 = fmaf(gz, w, ga1);
@@ -491,7 +502,7 @@ __global__ void __launch_bounds__(256) osc_finalize_kernel(
 static int pick_R(int hop, int prefer) {
     for (int R = prefer; R >= 4; R >>= 1)
         if (hop % (2 * R) == 0 && hop / R <= (R >= 16 ? 256 : 512) && hop / R >= 32) return R;
-    if (hop / 2 <= 512) return 2;
+    if ((hop + 1) / 2 <= 512) return 2;
     for (int R = 4; R <= prefer; R <<= 1)
         if (hop % (2 * R) == 0 && hop / R <= 512) return R;
     return 0;
@@ -501,9 +512,9 @@ static int check_osc_shape(const char* fn, int B, int T, int K, int hop, int sam
     DDSP_REQUIRE(B >= 1 && B <= 65535, "%s: B=%d out of range [1,65535]", fn, B);
     DDSP_REQUIRE(T >= 1, "%s: T=%d must be >= 1", fn, T);
     DDSP_REQUIRE(K >= 1 && K <= 4096, "%s: K=%d out of range [1,4096]", fn, K);
-    DDSP_REQUIRE(hop >= 2 && (hop % 2) == 0, "%s: hop=%d must be even and >= 2", fn, hop);
+    DDSP_REQUIRE(hop >= 1, "%s: hop=%d must be >= 1", fn, hop);
     DDSP_REQUIRE(sample_rate >= 1, "%s: sample_rate=%d must be positive", fn, sample_rate);
-    DDSP_REQUIRE(pick_R(hop, 8) > 0, "%s: hop=%d too large for one CTA per segment (max 4096)", fn, hop);
+    DDSP_REQUIRE(pick_R(hop, 8) > 0, "%s: hop=%d too large for one CTA per segment (odd or 2 mod 4: max 1024, else 4096)", fn, hop);
     return 0;
 }
 
@@ -544,7 +555,7 @@ extern "C" int ddsp_osc_synthesize(const float* f0, const float* a, const void* 
     const dim3 grid(T + 1, B);
     const size_t smem = sizeof(float4) * ((K + 1) & ~1);
 #define LAUNCH_SYNTH(RP) \
-    osc_synth_kernel<RP><<<grid, hop / (2 * RP), smem, st>>>(S.cn, a, S.kact, S.seg, y, z_save, accumulate, T, K, hop)
+    osc_synth_kernel<RP><<<grid, (hop + 2 * RP - 1) / (2 * RP), smem, st>>>(S.cn, a, S.kact, S.seg, y, z_save, accumulate, T, K, hop)
     if (smem > 48 * 1024) {
         cudaError_t e = cudaSuccess;
         switch (R) {
@@ -576,7 +587,7 @@ extern "C" int ddsp_osc_forward(const float* f0, const float* c, const float* a,
 template <int RP>
 static int launch_grad(const float* g, const float* a, const float* z, const OscState& S, float2* gseg, float2* gaseg, int B,
                        int T, int K, int hop, cudaStream_t st) {
-    const int NT = hop / (2 * RP);
+    const int NT = (hop + 2 * RP - 1) / (2 * RP);
     const size_t smem = sizeof(float) * GRAD_CH * (((2 * NT + 3) & ~3) + 4);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(osc_grad_kernel<RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -654,7 +665,7 @@ __global__ void __launch_bounds__(256) osc_live_kernel(const float* __restrict__
     for (int r = g.r_lo + threadIdx.x; r < g.r_hi; r += blockDim.x) {
         const double rr = (double)(r + 1);
         const double theta = fma(g.du * rr, rr, fma(rr, g.uL, g.E));        // cycles, not wrapped
-        const float w = ((float)r + 0.5f) / (float)hop;
+        const float w = ((float)r + seg_phi(hop)) / (float)hop;
         float acc = 0.f;
         for (int k = 0; k < kmax; ++k) {
             double ph = theta * (double)(k + 1);
@@ -674,7 +685,7 @@ __global__ void osc_live_state_kernel(const float* __restrict__ f0, const double
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= K) return;
     const Segment g = make_segment(T, T, hop, f0, phase0, inv_sr);
-    const double rr = (double)(hop / 2);                                     // r = hop/2 - 1 is the last sample
+    const double rr = (double)half_up(hop);                                  // r = ceil(hop/2) - 1 is the last sample
     const double theta = fma(g.du * rr, rr, fma(rr, g.uL, g.E));
     double ph = theta * (double)(k + 1) + (double)last_in[k] * 0.15915494309189533577;
     ph -= floor(ph);

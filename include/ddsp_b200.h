@@ -15,6 +15,8 @@
  *     calling thread).  Arguments are validated before anything is launched.
  *   - shapes: B voices, T frames, hop samples per frame, N = T*hop samples, K harmonics,
  *     NB noise bands (FIR length M = 2(NB-1) <= hop), L reverb taps.
+ *   - hop: any value the reference accepts, within the kernels' reach -- oscillator: hop % 4 == 0 up to 4096,
+ *     every other hop (odd ones included) up to 1024; filtered noise: 2..4096 (fast path when hop % 16 == 0).
  */
 #ifndef DDSP_B200_H
 #define DDSP_B200_H

@@ -25,7 +25,7 @@ def check(name, cfg, pairs, tol):
 for it in range(n_cases):
     try:
         # oscillator
-        hop = rnd.choice([2, 4, 6, 8, 10, 16, 24, 32, 48, 64, 100, 128, 256, 384, 512, 1024])
+        hop = rnd.choice([1, 2, 3, 4, 5, 6, 7, 8, 10, 15, 16, 24, 32, 48, 63, 64, 100, 128, 255, 256, 384, 441, 512, 1024])
         B, T, K = rnd.randint(1, 4), rnd.randint(1, 12), rnd.choice([1, 2, 3, 7, 16, 33, 100, 180, 256])
         sr = rnd.choice([4000, 16000, 44100, 48000])
         f0, c, a, H = O.synthetic_controls(B, T, K, 9, sr, hop, seed=it)

@@ -46,7 +46,11 @@ def test_golden_waveform_and_grads(golden, name):
                                           # a single frame, a single harmonic, the largest hops (16 samples per thread)
                                           (2, 3, 5, 8000, 2), (1, 4, 9, 8000, 6), (2, 5, 12, 16000, 10), (1, 1, 2, 16000, 512),
                                           (3, 1, 40, 48000, 16), (1, 3, 64, 48000, 1024), (1, 2, 30, 48000, 2048),
-                                          (1, 2, 17, 44100, 4096)])
+                                          (1, 2, 17, 44100, 4096),
+                                          # odd hops: a sample sits exactly on every frame centre (w = r/hop), the last
+                                          # sample pair of a segment is half masked; hop 1 = no upsampling at all
+                                          (2, 5, 12, 4000, 5), (1, 6, 40, 44100, 441), (2, 3, 7, 16000, 1), (1, 4, 9, 16000, 63),
+                                          (1, 3, 20, 48000, 1023), (2, 2, 6, 8000, 3)])
 def test_against_oracle(B, T, K, sr, hop):
     from oracle import ddsp_oracle as O
     f0, c, a, _ = O.synthetic_controls(B, T, K, 5, sr, hop, seed=100 + K)
@@ -105,6 +109,24 @@ def test_accumulate_into_out():
 def test_bad_arguments_raise():
     from ddsp_pytorch_b200 import ops
     with pytest.raises(RuntimeError):
-        ops.oscillator_bank(torch.ones(1, 3, 1).cuda(), torch.ones(1, 3, 4).cuda(), torch.ones(1, 3, 1).cuda(), 16000, 7)
+        ops.oscillator_bank(torch.ones(1, 3, 1).cuda(), torch.ones(1, 3, 4).cuda(), torch.ones(1, 3, 1).cuda(), 16000, 0)
+    with pytest.raises(RuntimeError):      # 2 mod 4 hops run two samples per thread: 1024 is their limit
+        ops.oscillator_bank(torch.ones(1, 3, 1).cuda(), torch.ones(1, 3, 4).cuda(), torch.ones(1, 3, 1).cuda(), 16000, 1026)
     with pytest.raises(RuntimeError):
         ops.oscillator_bank(torch.ones(1, 3, 1), torch.ones(1, 3, 4), torch.ones(1, 3, 1), 16000, 8)
+
+
+@pytest.mark.parametrize("hop,K,sr", [(5, 6, 4000), (441, 30, 44100), (64, 12, 16000)])
+def test_live_blocks_against_oracle(hop, K, sr):
+    """OscillatorBank.live over three blocks with carried phases, odd and even hops, against the fp64 oracle."""
+    import ddsp_pytorch_b200 as d
+    from oracle import ddsp_oracle as O
+    bank = d.OscillatorBank(d.Config(n_harmonics=K, sample_rate=sr, hop_length=hop)).cuda()
+    last = torch.zeros(K, dtype=torch.float64)
+    for blk in range(3):
+        f0, c, a, _ = O.synthetic_controls(1, 4, K, 5, sr, hop, seed=200 + blk)
+        want, last = O.oscillator_bank_live(f0.double(), c.double(), a.double(), last, K, sr, hop)
+        got = bank.live({"f0": f0.cuda(), "c": c.cuda(), "a": a.cuda()})
+        assert float((got.double().cpu() - want).abs().max()) <= WAVE_TOL
+        dphi = (bank.last_phases.double().cpu() - last).abs()
+        assert float(torch.minimum(dphi, 2 * np.pi - dphi).max()) <= 1e-4
