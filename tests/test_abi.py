@@ -56,7 +56,7 @@ def test_size_queries_and_argument_validation_need_no_gpu(lib_path):
     assert lib.ddsp_osc_state_bytes(0, 3, 4) == 0
     # validation happens before any CUDA call, so these fail cleanly on a GPU-less host
     with pytest.raises(RuntimeError, match="hop"):
-        _lib.call("ddsp_osc_forward", 1, 1, 1, 1, None, 1, 0, 1, 3, 4, 7, 16000, None)
+        _lib.call("ddsp_osc_forward", 1, 1, 1, 1, None, 1, 0, 1, 3, 4, 0, 16000, None)
     with pytest.raises(RuntimeError, match="null"):
         _lib.call("ddsp_osc_forward", None, None, None, None, None, None, 0, 1, 3, 4, 8, 16000, None)
     with pytest.raises(RuntimeError, match="FIR length"):
