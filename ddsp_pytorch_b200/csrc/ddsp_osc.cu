@@ -285,13 +285,14 @@ __global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_synth_kernel(
     }
 
     const float aL = a[fL], da = a[fR] - aL;
-    const float inv_hop = 1.0f / (float)hop, phi = seg_phi(hop);
+    const float inv_hop = 1.0f / (float)hop;
+    const float wb = ((float)r0 + seg_phi(hop)) * inv_hop;        // fraction of the thread's first sample between the frames
     float out[R], zs[R];
 #pragma unroll
     for (int j = 0; j < RP; ++j) {
         const float2 zP = __ffma2_rn(sg[j], Po[j], Pe[j]);     // sin(m theta) = sigma^m sin(m theta')
         const float2 zQ = __ffma2_rn(sg[j], Qo[j], Qe[j]);
-        const float w0 = ((float)(r0 + 2 * j) + phi) * inv_hop, w1 = ((float)(r0 + 2 * j + 1) + phi) * inv_hop;
+        const float w0 = fmaf((float)(2 * j), inv_hop, wb), w1 = fmaf((float)(2 * j + 1), inv_hop, wb);
         zs[2 * j] = fmaf(w0, zQ.x, zP.x);
         zs[2 * j + 1] = fmaf(w1, zQ.y, zP.y);
         out[2 * j] = fmaf(w0, da, aL) * zs[2 * j];
