@@ -227,7 +227,9 @@ __device__ __forceinline__ SegGeom seg_geom(int s, int T, int hop) {
 // synthesis: grid (T+1, B), hop/R threads, R consecutive samples per thread (R = 2*RP)
 // ------------------------------------------------------------------------------------------------
 template <int RP>
-__global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_synth_kernel(
+// register caps instead of launch bounds (they exclude each other): 8 samples per thread (the shipped hop 512) measured
+// fastest at 72 registers -- 76 uncapped, 3.32 -> 3.24 ms at cfg 4; 64 spills into the harmonic loop (3.51 ms)
+__global__ void __maxnreg__(RP == 4 ? 72 : (RP >= 8 ? 255 : 128)) osc_synth_kernel(
     const float* __restrict__ cn, const float* __restrict__ a, const int* __restrict__ kact,
     const SegFix* __restrict__ seg, float* __restrict__ y, float* __restrict__ z_save, int accumulate, int T, int K, int hop) {
     extern __shared__ __align__(16) float4 amp[];      // (c'_L, c'_L, dc', dc') per active harmonic: both halves of an FFMA2 operand
@@ -333,7 +335,8 @@ __global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_synth_kernel(
 constexpr int GRAD_CH = 32;
 
 template <int RP>
-__global__ void __launch_bounds__(RP >= 8 ? 256 : 512) osc_grad_kernel(
+// 16 samples per thread: 144 registers (158 uncapped; 128 spills) -- 3.78 -> 3.76 ms at cfg 4
+__global__ void __maxnreg__(RP >= 8 ? 144 : 128) osc_grad_kernel(
     const float* __restrict__ gup, const float* __restrict__ a, const float* __restrict__ z_save,
     const int* __restrict__ kact, const SegFix* __restrict__ seg, float2* __restrict__ gseg, float2* __restrict__ gaseg,
     int T, int K, int hop) {
