@@ -73,7 +73,8 @@ def bench_mss(args, dev):
 def bench_reverb(args, dev):
     import ddsp_pytorch_b200 as d
     out = []
-    for (B, N, sr) in ((16, 88064, 44100), (256, 192000, 48000)):
+    shapes = ((16, 88064, 44100), (256, 192000, 48000))
+    for (B, N, sr) in (shapes[1:] if args.reverb_big_only else shapes):
         conf = d.Config(sample_rate=sr, hop_length=512, n_harmonics=100, n_noise_filters=65)
         rv = d.Reverb(conf).to(dev)
         x = (torch.randn(B, N, generator=torch.Generator().manual_seed(3)) * 0.1).to(dev).requires_grad_(True)
@@ -117,8 +118,24 @@ def bench_path(args, dev):
         loss_fn(rv(dry), target).backward()
 
     ms = ev_time(step, args.reps)
+    # the eager step is ~35 launches in ~0.7 ms: host-launch bound on a slow host.  Replay it as a CUDA graph for the device time
+    # (ev_time above already ran the step on this side stream's allocator pool, so capture allocates nothing new)
+    graph_ms = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                step()
+        torch.cuda.current_stream().wait_stream(side)
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            step()
+        graph_ms = ev_time(gr.replay, args.reps)
+    except Exception as e:                              # report, do not hide: the eager number stands on its own
+        graph_ms = f"capture failed: {type(e).__name__}: {e}"[:200]
     return {"workload": f"cfg1' path: B={B} T={T} sr={sr} K={K} NB={NB}: osc + noise + reverb + 6-scale MSS, fwd+bwd",
-            "ms": ms, "samples_per_s": B * N / (ms * 1e-3)}
+            "ms": ms, "graph_replay_ms": graph_ms, "samples_per_s": B * N / (ms * 1e-3)}
 
 
 def bench_rt(args, dev):
@@ -236,6 +253,7 @@ def main():
     p.add_argument("--workloads", default="mss,reverb,path,rt")
     p.add_argument("--reps", type=int, default=20)
     p.add_argument("--rt-calls", type=int, default=2000)
+    p.add_argument("--reverb-big-only", action="store_true", help="reverb: only the B=256 shape (profiling runs)")
     args = p.parse_args()
     if not torch.cuda.is_available():
         raise RuntimeError("bench_extra.py needs a CUDA device; there is no CPU fallback")

@@ -221,24 +221,57 @@ __global__ void __launch_bounds__(MssFast<N>::THREADS, 512 / MssFast<N>::THREADS
     const float inv_ln2 = 1.4426950408889634f;
     double acc_lin = 0.0, acc_log = 0.0;
 
+    // d loss / d S_pred of one (bin, frame): both L1 terms accumulate, returns the factor that multiplies 2 X_pred.
+    // sp + eps and st + eps are normal positive numbers (eps > 0 is checked on the host), so the two log2 are single
+    // MUFU.LG2 (absolute error 2^-22 on a difference whose sign alone enters the gradient) and the quotient a
+    // MUFU.RCP + multiply (2 ulp) -- the library log2f / IEEE division were 23 % of the kernel's instructions
+    // (profiles/summary_r01g.md).
+    const float c_log = w_log * inv_ln2;
+    float it_lin = 0.f, it_log = 0.f;              // the <= 10 terms of one frame pair; the long sums are fp64
+    auto bin_grad = [&](float sp, float st) -> float {
+        const float dl = sp - st;
+        const float dq = __log2f(sp + eps) - __log2f(st + eps);
+        it_lin += fabsf(dl);
+        it_log += fabsf(dq);
+        const float sl = dl == 0.f ? 0.f : copysignf(w_lin, dl);
+        const float sq = dq == 0.f ? 0.f : copysignf(c_log, dq);
+        return sl + __fdividef(sq, sp + eps);
+    };
+
     for (int it = 0; it < P::ITERS; ++it) {
         const int fa = 2 * ((blockIdx.x * P::ITERS + it) * P::G + grp), fb = fa + 1;
         const bool live_a = fa < F, live_b = fb < F;   // dead groups still walk through every barrier
         const int pa = fa * hop - half, pb = fb * hop - half;
-        int ia[8], ib[8];                              // reflect-padded sample indices of the two frames
+        // frames that touch neither end of the signal (all but n/(2 hop) on each side) address it directly
+        const bool interior = pa >= 0 && pb + N <= Nsig;
+
+        // ---- gather both signals' samples of the two frames (the predicted ones wait in registers) ------------
+        float2 v[8];
+        float pra[8], prb[8];
+        if (interior) {
+            const float* st_ = xtb + pa + t;
+            const float* sp_ = xpb + pa + t;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            ia[q] = reflect_index(pa + t + q * T8, Nsig);
-            ib[q] = reflect_index(pb + t + q * T8, Nsig);
+            for (int q = 0; q < 8; ++q) {
+                v[q] = make_float2(st_[q * T8], st_[hop + q * T8]);
+                pra[q] = sp_[q * T8];
+                prb[q] = sp_[hop + q * T8];
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int ia = reflect_index(pa + t + q * T8, Nsig), ib = reflect_index(pb + t + q * T8, Nsig);
+                v[q] = make_float2(live_a ? xtb[ia] : 0.f, live_b ? xtb[ib] : 0.f);
+                pra[q] = live_a ? xpb[ia] : 0.f;
+                prb[q] = live_b ? xpb[ib] : 0.f;
+            }
         }
 
         // ---- true frames: power spectra of bins k = t + q*T8 (q < 4) and n/2, kept in registers ----------
         float St[2][5];
         {
-            float2 v[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
-                v[q] = make_float2(live_a ? win[q] * xtb[ia[q]] : 0.f, live_b ? win[q] * xtb[ib[q]] : 0.f);
+            for (int q = 0; q < 8; ++q) v[q] = make_float2(win[q] * v[q].x, win[q] * v[q].y);
             fft8_group<N, float, false>(v, smf, t);
             fft8_sync<N>();
 #pragma unroll
@@ -260,20 +293,17 @@ __global__ void __launch_bounds__(MssFast<N>::THREADS, 512 / MssFast<N>::THREADS
         // ---- predicted frames in fp64: their small bins decide d log2(S+eps)/dx ---------------------------
         double2 vd[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-            vd[q] = make_double2(live_a ? (double)win[q] * (double)xpb[ia[q]] : 0.0, live_b ? (double)win[q] * (double)xpb[ib[q]] : 0.0);
+        for (int q = 0; q < 8; ++q) vd[q] = make_double2((double)win[q] * (double)pra[q], (double)win[q] * (double)prb[q]);
         fft8_group<N, double, false>(vd, smd, t);
         fft8_sync<N>();
 #pragma unroll
         for (int q = 0; q < 8; ++q) smd[fft8_pad<double>(t + q * T8)] = vd[q];
         fft8_sync<N>();
-        float2 Yk[5], Yn[5];
+        float2 Yk[5], Yn[4];
 #pragma unroll
-        for (int q = 0; q < 5; ++q) {
-            Yk[q] = Yn[q] = make_float2(0.f, 0.f);
-            if (q == 4 && t != 0) continue;            // bin n/2 belongs to thread 0
-            const int k = q < 4 ? t + q * T8 : half;
-            const double2 zk = q < 4 ? vd[q] : smd[fft8_pad<double>(half)];
+        for (int q = 0; q < 4; ++q) {
+            const int k = t + q * T8;
+            const double2 zk = vd[q];
             const double2 zn = smd[fft8_pad<double>((N - k) & (N - 1))];
             const double xr[2] = {0.5 * (zk.x + zn.x), 0.5 * (zk.y + zn.y)};
             const double xi[2] = {0.5 * (zk.y - zn.y), -0.5 * (zk.x - zn.x)};
@@ -282,44 +312,59 @@ __global__ void __launch_bounds__(MssFast<N>::THREADS, 512 / MssFast<N>::THREADS
             for (int e = 0; e < 2; ++e) {
                 G[e] = make_float2(0.f, 0.f);
                 if (e == 0 ? live_a : live_b) {
-                    const float sp = (float)(xr[e] * xr[e] + xi[e] * xi[e]), st = St[e][q];          // power=2 spectrogram
-                    const float dl = sp - st;
-                    const float dq = log2f(sp + eps) - log2f(st + eps);
-                    acc_lin += (double)fabsf(dl);
-                    acc_log += (double)fabsf(dq);
-                    const float sl = (dl > 0.f) - (dl < 0.f), sq = (dq > 0.f) - (dq < 0.f);
-                    const float gs_ = w_lin * sl + w_log * sq * inv_ln2 / (sp + eps);               // d loss / d S_pred
-                    G[e] = make_float2(2.f * (float)xr[e] * gs_, 2.f * (float)xi[e] * gs_);          // d loss / d X_pred
+                    const float gs_ = 2.f * bin_grad((float)(xr[e] * xr[e] + xi[e] * xi[e]), St[e][q]);   // power=2 spectrogram
+                    G[e] = make_float2((float)xr[e] * gs_, (float)xi[e] * gs_);                           // d loss / d X_pred
                 }
             }
             // x-gradient of a frame = w * Re sum_{k<=n/2} G_k e^{+i 2 pi jk/n}: Hermitian-extend G (halved off the
             // edges) so the inverse transform is real, and carry the two frames as real / imaginary part
-            if (k == 0 || k == half) {
+            if (k == 0) {
                 Yk[q] = make_float2(G[0].x, G[1].x);
+                Yn[q] = make_float2(0.f, 0.f);
             } else {
                 Yk[q] = make_float2(0.5f * (G[0].x - G[1].y), 0.5f * (G[0].y + G[1].x));
                 Yn[q] = make_float2(0.5f * (G[0].x + G[1].y), 0.5f * (G[1].x - G[0].y));
             }
         }
+        // bin n/2 (real for both frames): thread 0 of the group, one pass for the two frames' values of Z[n/2]
+        Yk[4] = make_float2(0.f, 0.f);
+        if (t == 0) {
+            const double2 zh = smd[fft8_pad<double>(half)];          // Xa[n/2] = zh.x, Xb[n/2] = zh.y
+            float ga = 0.f, gb = 0.f;
+            if (live_a) ga = 2.f * (float)zh.x * bin_grad((float)(zh.x * zh.x), St[0][4]);
+            if (live_b) gb = 2.f * (float)zh.y * bin_grad((float)(zh.y * zh.y), St[1][4]);
+            Yk[4] = make_float2(ga, gb);
+        }
+        acc_lin += (double)it_lin;
+        acc_log += (double)it_log;
+        it_lin = it_log = 0.f;
         fft8_sync<N>();                                // everyone has read the fp64 spectra
         if (gxb) {
 #pragma unroll
-            for (int q = 0; q < 5; ++q) {
-                if (q == 4 && t != 0) continue;
-                const int k = q < 4 ? t + q * T8 : half;
+            for (int q = 0; q < 4; ++q) {
+                const int k = t + q * T8;
                 smf[fft8_pad<float>(k)] = Yk[q];
-                if (k != 0 && k != half) smf[fft8_pad<float>(N - k)] = Yn[q];
+                if (k != 0) smf[fft8_pad<float>(N - k)] = Yn[q];
             }
+            if (t == 0) smf[fft8_pad<float>(half)] = Yk[4];
             fft8_sync<N>();
-            float2 v[8];
 #pragma unroll
             for (int q = 0; q < 8; ++q) v[q] = smf[fft8_pad<float>(t + q * T8)];
             fft8_sync<N>();
             fft8_group<N, float, true>(v, smf, t);
+            if (interior) {
+                float* g_ = gxb + pa + t;
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                if (live_a) atomicAdd(&gxb[ia[q]], v[q].x * win[q]);
-                if (live_b) atomicAdd(&gxb[ib[q]], v[q].y * win[q]);
+                for (int q = 0; q < 8; ++q) {
+                    atomicAdd(g_ + q * T8, v[q].x * win[q]);
+                    atomicAdd(g_ + hop + q * T8, v[q].y * win[q]);
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    if (live_a) atomicAdd(&gxb[reflect_index(pa + t + q * T8, Nsig)], v[q].x * win[q]);
+                    if (live_b) atomicAdd(&gxb[reflect_index(pb + t + q * T8, Nsig)], v[q].y * win[q]);
+                }
             }
             fft8_sync<N>();                            // the inverse transform's last exchange is read
         }
@@ -395,7 +440,9 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
         const float* wptr = windows_host ? windows_host[s] : nullptr;
         double* terms = loss_terms + 1 + 2 * s;
         int rc = -1;
-        switch (n) {
+        // the register-tiled kernels take log2 / reciprocal of S + eps with MUFU: that needs a normal eps (the reference's
+        // default is 1e-7); eps = 0 or denormal goes through the generic kernel with the library functions
+        if (eps >= 1.17549435e-38f) switch (n) {
 #define MSS_CASE(NN) case NN: rc = launch_mss_fast<NN>(x_pred, x_true, loss_terms, terms, gx, wptr, B, N, hop, F, 1.0 / cnt, (double)alpha, eps, st); break
             MSS_CASE(8); MSS_CASE(16); MSS_CASE(32); MSS_CASE(64); MSS_CASE(128); MSS_CASE(256);
             MSS_CASE(512); MSS_CASE(1024); MSS_CASE(2048); MSS_CASE(4096);
