@@ -22,8 +22,7 @@ constexpr int CONV_P = 2048;            // new samples per block
 constexpr int CONV_N2 = 2 * CONV_P;     // FFT size
 constexpr int CONV_THREADS = 512;
 constexpr int GIR_CHUNKS = 32;          // partial sums over voice pairs kept apart for a fixed-order reduction
-constexpr int GIR_NP = 24;
-constexpr int GIR_PF = 6;              // prefetch depth of the gir walk (divides GIR_NP)              // IR partitions handled per pass of the gir kernel
+constexpr int GIR_NP = 24;             // IR partitions handled per pass of the gir kernel
 
 struct ConvPlan {
     int B2, nblk, np;
@@ -112,7 +111,7 @@ __global__ void __launch_bounds__(1024) reverb_impulse_bwd_kernel(const float* _
 //   halves = 1 with block index i = j+1: first half only ([h_j, 0], an IR partition; single real signal).
 // reverse != 0 reads the signals back to front (for gx).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(CONV_THREADS) conv_spectra_kernel(const float* __restrict__ x, float2* __restrict__ S, int B,
+__global__ void __launch_bounds__(CONV_THREADS, 3) conv_spectra_kernel(const float* __restrict__ x, float2* __restrict__ S, int B,
                                                                     int N, int nblk, int halves, int reverse, int blk_shift) {
     extern __shared__ __align__(16) float2 fsm[];      // exchange buffer of the register-tiled FFT
     const int i = blockIdx.x, b2 = blockIdx.y, tid = threadIdx.x;
@@ -140,43 +139,74 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_spectra_kernel(const float*
     for (int q = 0; q < 8; ++q) dst[tid + q * CONV_THREADS] = v[q];
 }
 
-// Y[b2,i,k] (+)= sum_{j<MAC_NP} H[jg+j,k] X[b2,i-jg-j,k]: one thread per (frequency bin, voice pair) walks the blocks
-// in order with the last MAC_NP input spectra of its bin in a register ring (static indices: the walk is unrolled
-// MAC_NP blocks at a time), so every X and H value is read from memory exactly once.
+// Y[b2,i,k] (+)= sum_{j<MAC_NP} H[jg+j,k] X[b2,i-jg-j,k].  Two adjacent lanes share a (frequency bin, voice pair): lane
+// parity s takes the partitions jg + s*MAC_NPT + [0, MAC_NPT) and walks the blocks in order with the last MAC_NPT input
+// spectra of ITS lag range in a register ring (static indices: the walk is unrolled MAC_NPT blocks at a time); the two
+// partial sums meet in one shuffle.  Every H value is read once, every X value twice (the second time MAC_NPT blocks
+// later, from L2).  One thread per bin with all 24 partitions needed 199 registers (8 warps per SM) and ptxas serialised
+// its accumulation chains: 42 % FMA-pipe utilisation, 38 % of warp samples in fixed-latency wait (profiles/summary_r01g.md).
 constexpr int MAC_NP = 24;
+constexpr int MAC_NPT = MAC_NP / 2;
 constexpr int MAC_THREADS = 128;
+constexpr int MAC_BINS = MAC_THREADS / 2;          // bins per CTA of conv_mac_kernel
 
-__global__ void __launch_bounds__(MAC_THREADS) conv_mac_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
-                                                               float2* __restrict__ Y, int nblk, int np, int jg, int accumulate) {
-    const int k = blockIdx.x * MAC_THREADS + threadIdx.x, b2 = blockIdx.y;
-    float2 h[MAC_NP], ring[MAC_NP];
+// One round of the walk = MAC_NPT consecutive blocks i0 .. i0+MAC_NPT-1.  prev / cur hold this lane's input spectra of the
+// previous / current round (cur[u] = X[i0 + u - jb]), so output u needs cur[u], cur[u-1], .., cur[0], prev[NPT-1], .., prev[u+1]
+// -- all static register indices; nxt receives the round after this one while the FMAs run.
+__device__ __forceinline__ void mac_round(const float2 (&prev)[MAC_NPT], const float2 (&cur)[MAC_NPT], float2 (&nxt)[MAC_NPT],
+                                          const float2 (&h)[MAC_NPT], const float2* __restrict__ xs, float* __restrict__ yf,
+                                          int i0, int jb, int nblk, int s, int accumulate) {
 #pragma unroll
-    for (int j = 0; j < MAC_NP; ++j) {
-        h[j] = (jg + j < np) ? Hf[(size_t)(jg + j) * CONV_N2 + k] : make_float2(0.f, 0.f);
-        ring[j] = make_float2(0.f, 0.f);
+    for (int u = 0; u < MAC_NPT; ++u) {
+        const int in = i0 + MAC_NPT + u, ix = in - jb;
+        nxt[u] = (in < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
     }
-    const float2* xs = S + (size_t)b2 * nblk * CONV_N2 + k;
-    float2* ys = Y + (size_t)b2 * nblk * CONV_N2 + k;
-    for (int i0 = jg; i0 < nblk; i0 += MAC_NP) {
-        float2 nxt[MAC_NP];
 #pragma unroll
-        for (int u = 0; u < MAC_NP; ++u)
-            nxt[u] = (i0 + u < nblk) ? xs[(size_t)(i0 + u - jg) * CONV_N2] : make_float2(0.f, 0.f);
+    for (int u = 0; u < MAC_NPT; ++u) {
+        const int i = i0 + u;                          // warp-uniform
+        if (i < nblk) {
+            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);          // four independent FMA chains
 #pragma unroll
-        for (int u = 0; u < MAC_NP; ++u) {
-            const int i = i0 + u;
-            if (i < nblk) {
-                ring[u] = nxt[u];
-                float2 acc = accumulate ? ys[(size_t)i * CONV_N2] : make_float2(0.f, 0.f);
-#pragma unroll
-                for (int j = 0; j < MAC_NP; ++j) {
-                    const float2 xv = ring[(u - j + MAC_NP) % MAC_NP], hv = h[j];
-                    acc.x = fmaf(xv.x, hv.x, fmaf(-xv.y, hv.y, acc.x));
-                    acc.y = fmaf(xv.x, hv.y, fmaf(xv.y, hv.x, acc.y));
-                }
-                ys[(size_t)i * CONV_N2] = acc;
+            for (int j = 0; j < MAC_NPT; ++j) {
+                const float2 xv = (u - j >= 0) ? cur[(u - j + MAC_NPT) % MAC_NPT] : prev[(u - j + MAC_NPT) % MAC_NPT], hv = h[j];
+                a0.x = fmaf(xv.x, hv.x, a0.x);
+                a1.x = fmaf(-xv.y, hv.y, a1.x);
+                a0.y = fmaf(xv.x, hv.y, a0.y);
+                a1.y = fmaf(xv.y, hv.x, a1.y);
             }
+            // lane s keeps component s of the sum over both lanes' partitions and stores that float: no divergent store
+            const float re = a0.x + a1.x, im = a0.y + a1.y;
+            float mine = (s ? im : re) + __shfl_xor_sync(0xffffffffu, s ? re : im, 1);
+            float* dst = yf + (size_t)i * (2 * CONV_N2);
+            if (accumulate) mine += *dst;
+            *dst = mine;
         }
+    }
+}
+
+__global__ void __launch_bounds__(MAC_THREADS, 4) conv_mac_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
+                                                                  float2* __restrict__ Y, int nblk, int np, int jg, int accumulate) {
+    const int s = threadIdx.x & 1;
+    const int k = blockIdx.x * MAC_BINS + (threadIdx.x >> 1), b2 = blockIdx.y;
+    const int jb = jg + s * MAC_NPT;               // first partition of this lane
+    float2 h[MAC_NPT], ra[MAC_NPT], rb[MAC_NPT], rc[MAC_NPT];
+    const float2* xs = S + (size_t)b2 * nblk * CONV_N2 + k;
+    float* yf = reinterpret_cast<float*>(Y + (size_t)b2 * nblk * CONV_N2 + k) + s;
+#pragma unroll
+    for (int j = 0; j < MAC_NPT; ++j) {
+        h[j] = (jb + j < np) ? Hf[(size_t)(jb + j) * CONV_N2 + k] : make_float2(0.f, 0.f);
+        ra[j] = make_float2(0.f, 0.f);
+        const int ix = jg + j - jb;                // the first round's spectra
+        rb[j] = (jg + j < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
+    }
+    // software pipeline over rounds with the three register sets taking turns as previous / current / incoming spectra (no
+    // copies); with the loads issued and consumed in the same step the kernel sat at 2.1 TB/s whatever its arithmetic looked like
+    for (int i0 = jg; i0 < nblk; i0 += 3 * MAC_NPT) {
+        mac_round(ra, rb, rc, h, xs, yf, i0, jb, nblk, s, accumulate);
+        if (i0 + MAC_NPT >= nblk) break;
+        mac_round(rb, rc, ra, h, xs, yf, i0 + MAC_NPT, jb, nblk, s, accumulate);
+        if (i0 + 2 * MAC_NPT >= nblk) break;
+        mac_round(rc, ra, rb, h, xs, yf, i0 + 2 * MAC_NPT, jb, nblk, s, accumulate);
     }
 }
 
@@ -205,54 +235,71 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_ifft_kernel(const float2* _
 
 // ------------------------------------------------------------------------------------------------
 // gradient of the kernel:  gir[jP+q] = Re IFFT( sum_{b2,i} conj(X[b2,i-j]) * Gt[b2,i] )[q] / 4096,  q < P
-// Thread = frequency bin; CTA (bin tile, voice-pair chunk) walks its voice pairs and blocks, holding one
-// accumulator per IR partition.  Chunk partials are summed in a fixed order by the finish kernel.
+// Two adjacent lanes share a frequency bin: lane parity s accumulates the partitions jg + s*GIR_NPT + [0, GIR_NPT).  A CTA
+// (bin tile, voice-pair chunk) walks its voice pairs and blocks in rounds of GIR_NPT blocks; the lane's input spectra of the
+// previous / current / next round sit in three register sets that take turns (static indices, no copies), the gradient
+// spectra of the next round are requested a round ahead.  Chunk partials are summed in a fixed order by the finish kernel.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(MAC_THREADS) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
-                                                               float2* __restrict__ part, int B2, int nblk, int np, int jg) {
-    const int k = blockIdx.x * MAC_THREADS + threadIdx.x;
-    const int c = blockIdx.y, nchunks = gridDim.y;
-    const int per = (B2 + nchunks - 1) / nchunks;
-    const int b_lo = c * per, b_hi = min(B2, b_lo + per);
-    float2 acc[GIR_NP], ring[GIR_NP];
+constexpr int GIR_NPT = GIR_NP / 2;
+
+// cur[u] = X[i0 + u - jb], g[u] = G[i0 + u]; acc[j] += g[u] * conj(X[i0 + u - jb - j])
+__device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], const float2 (&cur)[GIR_NPT], float2 (&nxt)[GIR_NPT],
+                                          float2 (&g)[GIR_NPT], float2 (&acc)[GIR_NPT], const float2* __restrict__ xs,
+                                          const float2* __restrict__ gs, int i0, int jb, int nblk) {
+    float2 gn[GIR_NPT];
 #pragma unroll
-    for (int j = 0; j < GIR_NP; ++j) acc[j] = make_float2(0.f, 0.f);
-    for (int b2 = b_lo; b2 < b_hi; ++b2) {
-        const float2* xs = Xf + (size_t)b2 * nblk * CONV_N2 + k;
-        const float2* gs = Gf + (size_t)b2 * nblk * CONV_N2 + k;
+    for (int u = 0; u < GIR_NPT; ++u) {
+        const int in = i0 + GIR_NPT + u, ix = in - jb;
+        nxt[u] = (in < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
+        gn[u] = in < nblk ? gs[(size_t)in * CONV_N2] : make_float2(0.f, 0.f);
+    }
 #pragma unroll
-        for (int j = 0; j < GIR_NP; ++j) ring[j] = make_float2(0.f, 0.f);
-        // ring slot u holds X[i - jg] of the block i = i0 + u being visited; slot (u - j) mod NP then holds X[i - jg - j]
-        for (int i0 = jg; i0 < nblk; i0 += GIR_NP) {
+    for (int u = 0; u < GIR_NPT; ++u) {
+        const float2 gv = g[u];                        // zero past the last block: nothing to guard
 #pragma unroll
-            for (int u0 = 0; u0 < GIR_NP; u0 += GIR_PF) {
-                float2 nx[GIR_PF], ng[GIR_PF];          // loads of GIR_PF blocks in flight together
-#pragma unroll
-                for (int v = 0; v < GIR_PF; ++v) {
-                    const int i = i0 + u0 + v;
-                    nx[v] = i < nblk ? xs[(size_t)(i - jg) * CONV_N2] : make_float2(0.f, 0.f);
-                    ng[v] = i < nblk ? gs[(size_t)i * CONV_N2] : make_float2(0.f, 0.f);
-                }
-#pragma unroll
-                for (int v = 0; v < GIR_PF; ++v) {
-                    const int u = u0 + v;
-                    if (i0 + u < nblk) {
-                        ring[u] = nx[v];
-                        const float2 g = ng[v];
-#pragma unroll
-                        for (int j = 0; j < GIR_NP; ++j) {
-                            const float2 xv = ring[(u - j + GIR_NP) % GIR_NP];      // g * conj(x)
-                            acc[j].x = fmaf(g.x, xv.x, fmaf(g.y, xv.y, acc[j].x));
-                            acc[j].y = fmaf(g.y, xv.x, fmaf(-g.x, xv.y, acc[j].y));
-                        }
-                    }
-                }
-            }
+        for (int j = 0; j < GIR_NPT; ++j) {
+            const float2 xv = (u - j >= 0) ? cur[(u - j + GIR_NPT) % GIR_NPT] : prev[(u - j + GIR_NPT) % GIR_NPT];
+            acc[j].x = fmaf(gv.x, xv.x, fmaf(gv.y, xv.y, acc[j].x));
+            acc[j].y = fmaf(gv.y, xv.x, fmaf(-gv.x, xv.y, acc[j].y));
         }
     }
 #pragma unroll
-    for (int j = 0; j < GIR_NP; ++j)
-        if (jg + j < np) part[((size_t)c * np + jg + j) * CONV_N2 + k] = acc[j];
+    for (int u = 0; u < GIR_NPT; ++u) g[u] = gn[u];
+}
+
+__global__ void __launch_bounds__(MAC_THREADS, 3) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
+                                                                  float2* __restrict__ part, int B2, int nblk, int np, int jg) {
+    const int s = threadIdx.x & 1;
+    const int k = blockIdx.x * MAC_BINS + (threadIdx.x >> 1);
+    const int jb = jg + s * GIR_NPT;
+    const int c = blockIdx.y, nchunks = gridDim.y;
+    const int per = (B2 + nchunks - 1) / nchunks;
+    const int b_lo = c * per, b_hi = min(B2, b_lo + per);
+    float2 acc[GIR_NPT];
+#pragma unroll
+    for (int j = 0; j < GIR_NPT; ++j) acc[j] = make_float2(0.f, 0.f);
+    for (int b2 = b_lo; b2 < b_hi; ++b2) {
+        const float2* xs = Xf + (size_t)b2 * nblk * CONV_N2 + k;
+        const float2* gs = Gf + (size_t)b2 * nblk * CONV_N2 + k;
+        float2 ra[GIR_NPT], rb[GIR_NPT], rc[GIR_NPT], g[GIR_NPT];
+#pragma unroll
+        for (int u = 0; u < GIR_NPT; ++u) {
+            const int i = jg + u, ix = i - jb;
+            ra[u] = make_float2(0.f, 0.f);
+            rb[u] = (i < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
+            g[u] = i < nblk ? gs[(size_t)i * CONV_N2] : make_float2(0.f, 0.f);
+        }
+        for (int i0 = jg; i0 < nblk; i0 += 3 * GIR_NPT) {
+            gir_round(ra, rb, rc, g, acc, xs, gs, i0, jb, nblk);
+            if (i0 + GIR_NPT >= nblk) break;
+            gir_round(rb, rc, ra, g, acc, xs, gs, i0 + GIR_NPT, jb, nblk);
+            if (i0 + 2 * GIR_NPT >= nblk) break;
+            gir_round(rc, ra, rb, g, acc, xs, gs, i0 + 2 * GIR_NPT, jb, nblk);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < GIR_NPT; ++j)
+        if (jb + j < np) part[((size_t)c * np + jb + j) * CONV_N2 + k] = acc[j];
 }
 
 __global__ void __launch_bounds__(CONV_THREADS) conv_gir_finish_kernel(const float2* __restrict__ part, float* __restrict__ gir,
@@ -312,6 +359,26 @@ static int conv_setup(cudaStream_t st) {
     return 0;
 }
 
+// voice-pair chunks of the kernel-gradient walk: as many as fit ONE wave of resident CTAs (the 32-chunk grid was 2.3 waves
+// of 3 CTAs per SM, the last one a third full), evened out; GIR_CHUNKS bounds the partial-sum scratch
+static int gir_chunk_count(int B2) {
+    static int slots_cache[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (slots_cache[dev] == 0) {
+        int sms = 148, per_sm = 3;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv_gir_kernel, MAC_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 3;
+        const int s = sms * per_sm / (CONV_N2 / MAC_BINS);
+        slots_cache[dev] = s < 1 ? 1 : s;
+    }
+    int n = slots_cache[dev];
+    if (n > GIR_CHUNKS) n = GIR_CHUNKS;
+    if (n > B2) n = B2;
+    const int per = (B2 + n - 1) / n;
+    return (B2 + per - 1) / per;
+}
+
 static int check_conv(const char* fn, int B, int N, int Lk) {
     DDSP_REQUIRE(B >= 1 && B <= 2 * 65535, "%s: B=%d out of range", fn, B);
     DDSP_REQUIRE(N >= 1 && Lk >= 1, "%s: N=%d, Lk=%d must be positive", fn, N, Lk);
@@ -362,7 +429,7 @@ extern "C" int ddsp_conv_forward(const float* x, const float* ir, float* y, void
     DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
     float2* S1 = reinterpret_cast<float2*>(base + p.off_S1);
     for (int jg = 0; jg < p.np; jg += MAC_NP) {
-        conv_mac_kernel<<<dim3(CONV_N2 / MAC_THREADS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+        conv_mac_kernel<<<dim3(CONV_N2 / MAC_BINS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
         DDSP_CHECK_LAUNCH("conv_mac_kernel");
     }
     conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, y, B, N, p.nblk, 0);
@@ -393,9 +460,9 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         }
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S1, B, N, p.nblk, 2, 0, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(g tail)");
-        const int nchunks = p.B2 < GIR_CHUNKS ? p.B2 : GIR_CHUNKS;
+        const int nchunks = gir_chunk_count(p.B2);
         for (int jg = 0; jg < p.np; jg += GIR_NP) {
-            conv_gir_kernel<<<dim3(CONV_N2 / MAC_THREADS, nchunks), MAC_THREADS, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
+            conv_gir_kernel<<<dim3(CONV_N2 / MAC_BINS, nchunks), MAC_THREADS, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
             DDSP_CHECK_LAUNCH("conv_gir_kernel");
         }
         cudaError_t e = cudaMemsetAsync(gir, 0, sizeof(float) * (size_t)Lk, st);
@@ -411,7 +478,7 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S0, B, N, p.nblk, 3, 1, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(flip g)");
         for (int jg = 0; jg < p.np; jg += MAC_NP) {
-            conv_mac_kernel<<<dim3(CONV_N2 / MAC_THREADS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+            conv_mac_kernel<<<dim3(CONV_N2 / MAC_BINS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
             DDSP_CHECK_LAUNCH("conv_mac_kernel(gx)");
         }
         conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, gx, B, N, p.nblk, 1);
