@@ -353,6 +353,13 @@ def run_b200(args):
                     "work": f"{flops_per_hs:g} flop x {active:.4g} active harmonic-samples on this rank "
                             f"(nominal K would be {Bl * N * K:.4g}; Nyquist-masked harmonics are skipped)",
                     "achieved_if_nominal_K": flops_per_hs * Bl * N * K / (kernels_ms[dom] * 1e-3) / 1e12,
+                    # what the kernel itself executes: 4 FMA-pipe lane operations per harmonic-sample in either direction (3 FMA +
+                    # 1 add, issued as packed FFMA2/FADD2 pairs; counted as 8 flop of pipe capacity) -- fewer than SURVEY's
+                    # count for the backward, so `frac` above overstates the pipe's occupancy; this is the figure to compare
+                    # with ncu's sm__pipe_fma_cycles_active
+                    "executed": {"pipe_flop_per_harmonic_sample": 8.0,
+                                 "tflops": 8.0 * active / (kernels_ms[dom] * 1e-3) / 1e12,
+                                 "frac_of_peak": 8.0 * active / (kernels_ms[dom] * 1e-3) / 1e12 / fp32_peak},
                     "hbm": {"algorithmic_bytes": 4.0 * (Bl * N * 2 + Bl * T * (K + 2)),
                             "achieved_GBps": 4.0 * (Bl * N * 2 + Bl * T * (K + 2)) / (kernels_ms[dom] * 1e-3) / 1e9,
                             "peak_GBps": peaks.get("hbm_gbs")}}

@@ -152,6 +152,26 @@ def test_mss_gradient_on_noise_like_input(N, n):
     assert err <= 2e-6
 
 
+@pytest.mark.parametrize("eps", [1e-7, 1e-3, 1e-39])
+def test_mss_eps_values(eps):
+    """The register-tiled kernels evaluate log2(S+eps) and 1/(S+eps) with MUFU for a normal eps; a denormal eps
+    (1e-39) takes the generic kernel with the library functions.  Both against the fp64 oracle at the same eps."""
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(77)
+    xp, xt = torch.randn(3, 3000, generator=gen) * 0.3, torch.randn(3, 3000, generator=gen) * 0.3
+    xpd = xp.double().requires_grad_(True)
+    want = O.mss_loss(xpd, xt.double(), [256, 64], eps=eps)
+    want.backward()
+    xpc = xp.cuda().requires_grad_(True)
+    got = ops.mss_loss(xpc, xt.cuda(), [256, 64], eps=eps)
+    got.backward()
+    assert abs(float(got) - float(want)) <= 1e-5 * float(want)
+    err = float((xpc.grad.double().cpu() - xpd.grad).norm() / xpd.grad.norm())
+    print(f"eps={eps:g}: grad rel l2 err {err:.2e}")
+    assert err <= 1e-4
+
+
 def test_mss_dict_inputs_and_identity():
     import ddsp_pytorch_b200 as d
     x = torch.randn(2, 4096).cuda() * 0.1
