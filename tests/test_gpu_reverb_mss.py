@@ -41,7 +41,10 @@ def test_reverb_golden(golden, name):
 
 
 @pytest.mark.parametrize("B,N,L", [(3, 9000, 5000), (2, 4096, 4096), (1, 2048, 44100), (5, 20000, 16000), (2, 6000, 2049),
-                                   (1, 100, 7)])
+                                   (1, 100, 7),
+                                   # 13 partitions (the second lane of a pair holds one), 25 and 28 partitions (a second MAC /
+                                   # kernel-gradient pass that accumulates onto the first)
+                                   (4, 30000, 26000), (3, 52000, 50000), (2, 60000, 56000)])
 def test_conv_against_oracle(B, N, L):
     from ddsp_pytorch_b200 import ops
     from oracle import ddsp_oracle as O
