@@ -53,19 +53,45 @@ __global__ void __launch_bounds__(PREP_THREADS) osc_prepare_kernel(
             float* cnr = cn + ((size_t)b * T + t) * K;
             float sum = 0.f;
             int last = 0;
-            for (int k = lane; k < K; k += 32) {
-                const bool masked = (float)(k + 1) * f > nyq;
-                const float v = masked ? 0.f : cr[k];
-                sum += v;
-                if (!masked) last = k + 1;
+            float vreg[8];                                  // K <= 256: the frame's row stays in registers between the two sweeps
+            if (K <= 256) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k = lane + 32 * i;
+                    const bool masked = (float)(k + 1) * f > nyq;
+                    vreg[i] = (k < K && !masked) ? cr[k] : 0.f;
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k = lane + 32 * i;
+                    if (k < K) {
+                        sum += vreg[i];
+                        if (!((float)(k + 1) * f > nyq)) last = k + 1;
+                    }
+                }
+            } else {
+                for (int k = lane; k < K; k += 32) {
+                    const bool masked = (float)(k + 1) * f > nyq;
+                    const float v = masked ? 0.f : cr[k];
+                    sum += v;
+                    if (!masked) last = k + 1;
+                }
             }
             sum = warp_sum(sum);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) last = max(last, __shfl_xor_sync(0xffffffffu, last, o));
             if (!(sum > 0.f)) last = K;                     // 0/0 or NaN frame: keep every harmonic so NaN propagates like :33
-            for (int k = lane; k < K; k += 32) {
-                const bool masked = (float)(k + 1) * f > nyq;
-                cnr[k] = (masked ? 0.f : cr[k]) / sum;
+            if (K <= 256) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int k = lane + 32 * i;
+                    if (k < K) cnr[k] = vreg[i] / sum;
+                }
+            } else {
+                for (int k = lane; k < K; k += 32) {
+                    const bool masked = (float)(k + 1) * f > nyq;
+                    cnr[k] = (masked ? 0.f : cr[k]) / sum;
+                }
             }
             if (lane == 0) {
                 csum[(size_t)b * T + t] = sum;
@@ -485,6 +511,7 @@ __global__ void __launch_bounds__(256) osc_finalize_kernel(
         return v;
     };
     float dot = 0.f;
+    // (a one-pass variant with the frame's values parked in registers and all loads in flight measured slower: 0.33 -> 0.39 ms)
     for (int k = lane; k < kt; k += 32) dot = fmaf(grad_cn(k), cnr[k], dot);
     dot = warp_sum(dot);
     for (int k = lane; k < K; k += 32) {
