@@ -186,7 +186,6 @@ struct MssFast {
     static constexpr int T8 = N / 8;                              // threads per frame pair
     static constexpr int THREADS = T8 > 128 ? T8 : 128;
     static constexpr int G = THREADS / T8;                        // frame pairs in flight per CTA
-    static constexpr int ITERS = N >= 1024 ? 2 : 4;               // frame pairs per group, sequentially
     static constexpr size_t group_bytes = sizeof(double2) * fft8_smem_elems(N);
     static constexpr size_t smem = group_bytes * G;
 };
@@ -196,18 +195,14 @@ __global__ void __launch_bounds__(MssFast<N>::THREADS, 512 / MssFast<N>::THREADS
                                                                       double* __restrict__ loss, double* __restrict__ terms,
                                                                       float* __restrict__ gx, const float* __restrict__ window,
                                                                       int Nsig, int hop, int F, double inv_count, double alpha_d,
-                                                                      float eps) {
+                                                                      float eps, int items_per_voice, long long n_items) {
     using P = MssFast<N>;
     constexpr int T8 = P::T8, half = N / 2;
     extern __shared__ __align__(16) unsigned char mss_raw[];
     __shared__ double red[2][P::THREADS / 32];
     const int tid = threadIdx.x, grp = tid / T8, t = tid % T8;
-    const int b = blockIdx.y;
     double2* smd = reinterpret_cast<double2*>(mss_raw + (size_t)grp * P::group_bytes);
     float2* smf = reinterpret_cast<float2*>(smd);
-    const float* xpb = xp + (size_t)b * Nsig;
-    const float* xtb = xt + (size_t)b * Nsig;
-    float* gxb = gx ? gx + (size_t)b * Nsig : nullptr;
 
     // the reference's window is the fp32 buffer of its Spectrogram module (mss_loss.py:23); use the caller's copy when
     // given so both sides window with the same values, else the periodic Hann
@@ -238,8 +233,15 @@ __global__ void __launch_bounds__(MssFast<N>::THREADS, 512 / MssFast<N>::THREADS
         return sl + __fdividef(sq, sp + eps);
     };
 
-    for (int it = 0; it < P::ITERS; ++it) {
-        const int fa = 2 * ((blockIdx.x * P::ITERS + it) * P::G + grp), fb = fa + 1;
+    // Work item = (voice, P::G consecutive frame pairs), one pair per thread group.  The grid is at most one wave of resident
+    // CTAs and every CTA strides over the items: with a fixed 2-4 items per CTA the small shapes ran 1.2-2.4 waves, the last
+    // one nearly empty (cfg 1': 704 CTAs on 592 slots, 40-50 us per scale for 25 us of work).
+    for (long long item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int b = (int)(item / items_per_voice), pblk = (int)(item % items_per_voice);
+        const float* xpb = xp + (size_t)b * Nsig;
+        const float* xtb = xt + (size_t)b * Nsig;
+        float* gxb = gx ? gx + (size_t)b * Nsig : nullptr;
+        const int fa = 2 * (pblk * P::G + grp), fb = fa + 1;
         const bool live_a = fa < F, live_b = fb < F;   // dead groups still walk through every barrier
         const int pa = fa * hop - half, pb = fb * hop - half;
         // frames that touch neither end of the signal (all but n/(2 hop) on each side) address it directly
@@ -392,9 +394,22 @@ static int launch_mss_fast(const float* xp, const float* xt, double* loss, doubl
         cudaError_t e = cudaFuncSetAttribute(mss_fast_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P::smem);
         DDSP_REQUIRE(e == cudaSuccess, "mss_fast_kernel: cannot reserve %zu B of shared memory: %s", (size_t)P::smem, cudaGetErrorString(e));
     }
-    const int per_cta = 2 * P::G * P::ITERS;
-    mss_fast_kernel<N><<<dim3((F + per_cta - 1) / per_cta, B), P::THREADS, P::smem, st>>>(xp, xt, loss, terms, gx, window, Nsig, hop, F,
-                                                                                          inv_count, alpha_d, eps);
+    static int slots_cache[64] = {0};                  // resident CTAs of this instantiation per device
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (slots_cache[dev] == 0) {
+        int sms = 148, per_sm = 1;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, mss_fast_kernel<N>, P::THREADS, P::smem) != cudaSuccess || per_sm < 1)
+            per_sm = 1;
+        slots_cache[dev] = sms * per_sm;
+    }
+    const int pairs = (F + 1) / 2;
+    const int items_per_voice = (pairs + P::G - 1) / P::G;
+    const long long n_items = (long long)B * items_per_voice;
+    const unsigned grid = (unsigned)(n_items < slots_cache[dev] ? n_items : slots_cache[dev]);
+    mss_fast_kernel<N><<<grid, P::THREADS, P::smem, st>>>(xp, xt, loss, terms, gx, window, Nsig, hop, F, inv_count, alpha_d, eps,
+                                                          items_per_voice, n_items);
     DDSP_CHECK_LAUNCH("mss_fast_kernel");
     return 0;
 }
