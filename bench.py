@@ -147,6 +147,29 @@ def cpu_measure(args, sh, steps: int, warmup: int):
             "ms_per_step": best * 1e3, "median_ms_per_step": statistics.median(times) * 1e3}
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """Keep the real stdout for the ONE JSON line and send everything else written to fd 1 (NCCL's version banner on the first
+    communicator, library chatter) to stderr."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    payload = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        sys.stdout.buffer.write(payload)
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, payload)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -163,7 +186,7 @@ def run_reference(args):
             "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -390,13 +413,14 @@ def run_b200(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args, sh), "clocks": clocks, "e2e": e2e, "gpu_launches": 6 * args.steps,
             "roofline": roofline, "roofline_fused": fused, "cpu_baseline": cpu, "kernels_ms": kernels_ms, "fp32_fma_peak_tflops_measured": fp32_peak, "rt_block_latency": rt}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a_ = parse_args()
+    claim_stdout()
     if a_.impl == "reference":
         run_reference(a_)
     else:
