@@ -32,3 +32,32 @@ def test_pipeline_matches_single_call():
     y = ops.filtered_noise(Hd, hop, seed=5, offset=1, voice_offset=7)
     y.backward(g.to(dev))
     assert torch.equal(outs[2], Hd.grad.cpu())
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_reduced_precision_inputs_are_cast_at_the_boundary(dtype):
+    """Under the reference's ``precision=16`` (train/train.py:50) the Controller hands c, a, H over in half precision: the ops
+    cast to fp32 at the autograd boundary, compute as for the same values in fp32 and return gradients in the
+    caller's dtype."""
+    from ddsp_pytorch_b200 import ops
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
+    B, T, K, NB, sr, hop = 2, 6, 40, 65, 16000, 512
+    f0, c, a, H = (t.cuda() for t in synthetic_controls(B, T, K, NB, sr, hop, seed=5))
+    g = torch.randn(B, T * hop, device="cuda")
+    lo = [t.to(dtype).requires_grad_(True) for t in (c, a, H)]
+    hi = [t.detach().float().requires_grad_(True) for t in lo]
+    outs = []
+    for cc, aa, HH in (lo, hi):
+        y = ops.filtered_noise(HH, hop, seed=3) + ops.oscillator_bank(f0, cc, aa, sr, hop)
+        y.backward(g)
+        outs.append(y.detach())
+    assert outs[0].dtype == torch.float32 and torch.equal(outs[0], outs[1])
+    for l, h in zip(lo, hi):
+        assert l.grad.dtype == dtype and l.grad.shape == l.shape
+        assert torch.equal(l.grad, h.grad.to(dtype))
+    xp = (torch.randn(2, 3000, device="cuda") * 0.1).to(dtype).requires_grad_(True)
+    xt = torch.randn(2, 3000, device="cuda") * 0.1
+    ops.mss_loss(xp, xt, [256, 64]).backward()
+    xp32 = xp.detach().float().requires_grad_(True)
+    ops.mss_loss(xp32, xt, [256, 64]).backward()
+    assert xp.grad.dtype == dtype and torch.equal(xp.grad, xp32.grad.to(dtype))
