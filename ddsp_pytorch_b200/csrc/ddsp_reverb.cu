@@ -242,16 +242,26 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_ifft_kernel(const float2* _
 // ------------------------------------------------------------------------------------------------
 constexpr int GIR_NPT = GIR_NP / 2;
 
-// cur[u] = X[i0 + u - jb], g[u] = G[i0 + u]; acc[j] += g[u] * conj(X[i0 + u - jb - j])
-__device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], const float2 (&cur)[GIR_NPT], float2 (&nxt)[GIR_NPT],
-                                          float2 (&g)[GIR_NPT], float2 (&acc)[GIR_NPT], const float2* __restrict__ xs,
-                                          const float2* __restrict__ gs, int i0, int jb, int nblk) {
-    float2 gn[GIR_NPT];
+// 8-byte asynchronous copy global -> shared; nbytes = 0 writes zeros without touching src (LDGSTS with zero fill)
+__device__ __forceinline__ void cp_async8(void* dst_smem, const void* src, int nbytes) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(nbytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int GIR_STAGES = 2;          // rounds staged in shared memory: the one being consumed + one in flight (48 KB: 4 CTAs per SM)
+constexpr size_t GIR_SMEM = sizeof(float2) * GIR_STAGES * 2 * GIR_NPT * MAC_THREADS;
+
+// One round: cur[u] = X[i0 + u - jb] and g[u] = G[i0 + u] come out of the thread's own staging slots;
+// acc[j] += g[u] * conj(X[i0 + u - jb - j]) with X[.. < round start] in prev (the previous round's cur).
+__device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], float2 (&cur)[GIR_NPT], float2 (&acc)[GIR_NPT],
+                                          const float2* __restrict__ slot) {
+    float2 g[GIR_NPT];
 #pragma unroll
     for (int u = 0; u < GIR_NPT; ++u) {
-        const int in = i0 + GIR_NPT + u, ix = in - jb;
-        nxt[u] = (in < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
-        gn[u] = in < nblk ? gs[(size_t)in * CONV_N2] : make_float2(0.f, 0.f);
+        cur[u] = slot[u * MAC_THREADS];
+        g[u] = slot[(GIR_NPT + u) * MAC_THREADS];
     }
 #pragma unroll
     for (int u = 0; u < GIR_NPT; ++u) {
@@ -263,40 +273,69 @@ __device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], const f
             acc[j].y = fmaf(gv.y, xv.x, fmaf(-gv.x, xv.y, acc[j].y));
         }
     }
-#pragma unroll
-    for (int u = 0; u < GIR_NPT; ++u) g[u] = gn[u];
 }
 
-__global__ void __launch_bounds__(MAC_THREADS, 3) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
+// The walk over (voice pair, round of GIR_NPT blocks) is one flat sequence of rounds.  Every thread copies the 2 x GIR_NPT
+// spectra values of a round into its own shared-memory slots with cp.async, GIR_STAGES - 1 rounds ahead of the one it
+// multiplies: the loads in flight cost no registers and no barrier (a slot is only ever read by the thread that filled it).
+// With the look-ahead held in registers (one round, 168 registers) the kernel spent 53 % of its warp samples on the long
+// scoreboard (profiles/summary_r01g.md).
+__global__ void __launch_bounds__(MAC_THREADS, 4) conv_gir_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Gf,
                                                                   float2* __restrict__ part, int B2, int nblk, int np, int jg) {
+    extern __shared__ __align__(16) float2 gir_sm[];   // [GIR_STAGES][2 * GIR_NPT][MAC_THREADS]
     const int s = threadIdx.x & 1;
     const int k = blockIdx.x * MAC_BINS + (threadIdx.x >> 1);
     const int jb = jg + s * GIR_NPT;
     const int c = blockIdx.y, nchunks = gridDim.y;
     const int per = (B2 + nchunks - 1) / nchunks;
     const int b_lo = c * per, b_hi = min(B2, b_lo + per);
-    float2 acc[GIR_NPT];
+    const int rpp = (nblk - jg + GIR_NPT - 1) / GIR_NPT;                 // rounds per voice pair
+    const int R = (b_hi > b_lo ? b_hi - b_lo : 0) * rpp;                 // rounds of this CTA
+    float2* mine = gir_sm + threadIdx.x;
+
+    auto issue = [&](int r) {                          // request round r into stage r % GIR_STAGES (an empty group past the end)
+        if (r < R) {
+            const int b2 = b_lo + r / rpp, i0 = jg + (r % rpp) * GIR_NPT;
+            // round base addresses; a zero-byte copy forms its source address but never reads it (lane 1's first rounds
+            // point in front of the pair's first block)
+            const long long row0 = (long long)b2 * nblk + i0;
+            const float2* xr = Xf + (row0 - jb) * CONV_N2 + k;
+            const float2* gr = Gf + row0 * CONV_N2 + k;
+            float2* slot = mine + (size_t)(r % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS);
 #pragma unroll
-    for (int j = 0; j < GIR_NPT; ++j) acc[j] = make_float2(0.f, 0.f);
-    for (int b2 = b_lo; b2 < b_hi; ++b2) {
-        const float2* xs = Xf + (size_t)b2 * nblk * CONV_N2 + k;
-        const float2* gs = Gf + (size_t)b2 * nblk * CONV_N2 + k;
-        float2 ra[GIR_NPT], rb[GIR_NPT], rc[GIR_NPT], g[GIR_NPT];
+            for (int u = 0; u < GIR_NPT; ++u) {
+                const int in = i0 + u;
+                cp_async8(slot + u * MAC_THREADS, xr + (size_t)u * CONV_N2, (in < nblk && in >= jb) ? 8 : 0);
+                cp_async8(slot + (GIR_NPT + u) * MAC_THREADS, gr + (size_t)u * CONV_N2, in < nblk ? 8 : 0);
+            }
+        }
+        cp_async_commit();
+    };
+
+    float2 acc[GIR_NPT], ra[GIR_NPT], rb[GIR_NPT];
 #pragma unroll
-        for (int u = 0; u < GIR_NPT; ++u) {
-            const int i = jg + u, ix = i - jb;
-            ra[u] = make_float2(0.f, 0.f);
-            rb[u] = (i < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
-            g[u] = i < nblk ? gs[(size_t)i * CONV_N2] : make_float2(0.f, 0.f);
+    for (int j = 0; j < GIR_NPT; ++j) acc[j] = ra[j] = rb[j] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int r = 0; r < GIR_STAGES - 1; ++r) issue(r);
+    for (int r = 0; r < R; r += 2) {
+        // even round of the pair: previous spectra in ra, current into rb; odd round: the other way round
+        issue(r + GIR_STAGES - 1);
+        cp_async_wait<GIR_STAGES - 1>();
+        if (r % rpp == 0) {
+#pragma unroll
+            for (int j = 0; j < GIR_NPT; ++j) ra[j] = make_float2(0.f, 0.f);      // a new voice pair starts with an empty history
         }
-        for (int i0 = jg; i0 < nblk; i0 += 3 * GIR_NPT) {
-            gir_round(ra, rb, rc, g, acc, xs, gs, i0, jb, nblk);
-            if (i0 + GIR_NPT >= nblk) break;
-            gir_round(rb, rc, ra, g, acc, xs, gs, i0 + GIR_NPT, jb, nblk);
-            if (i0 + 2 * GIR_NPT >= nblk) break;
-            gir_round(rc, ra, rb, g, acc, xs, gs, i0 + 2 * GIR_NPT, jb, nblk);
+        gir_round(ra, rb, acc, mine + (size_t)(r % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS));
+        if (r + 1 >= R) break;
+        issue(r + GIR_STAGES);
+        cp_async_wait<GIR_STAGES - 1>();
+        if ((r + 1) % rpp == 0) {
+#pragma unroll
+            for (int j = 0; j < GIR_NPT; ++j) rb[j] = make_float2(0.f, 0.f);
         }
+        gir_round(rb, ra, acc, mine + (size_t)((r + 1) % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS));
     }
+    cp_async_wait<0>();
 #pragma unroll
     for (int j = 0; j < GIR_NPT; ++j)
         if (jb + j < np) part[((size_t)c * np + jb + j) * CONV_N2 + k] = acc[j];
@@ -368,7 +407,8 @@ static int gir_chunk_count(int B2) {
     if (slots_cache[dev] == 0) {
         int sms = 148, per_sm = 3;
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv_gir_kernel, MAC_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 3;
+        cudaFuncSetAttribute(conv_gir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GIR_SMEM);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, conv_gir_kernel, MAC_THREADS, GIR_SMEM) != cudaSuccess || per_sm < 1) per_sm = 3;
         const int s = sms * per_sm / (CONV_N2 / MAC_BINS);
         slots_cache[dev] = s < 1 ? 1 : s;
     }
@@ -462,7 +502,7 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(g tail)");
         const int nchunks = gir_chunk_count(p.B2);
         for (int jg = 0; jg < p.np; jg += GIR_NP) {
-            conv_gir_kernel<<<dim3(CONV_N2 / MAC_BINS, nchunks), MAC_THREADS, 0, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
+            conv_gir_kernel<<<dim3(CONV_N2 / MAC_BINS, nchunks), MAC_THREADS, GIR_SMEM, st>>>(S0, S1, part, p.B2, p.nblk, p.np, jg);
             DDSP_CHECK_LAUNCH("conv_gir_kernel");
         }
         cudaError_t e = cudaMemsetAsync(gir, 0, sizeof(float) * (size_t)Lk, st);
