@@ -150,17 +150,25 @@ constexpr int MAC_NPT = MAC_NP / 2;
 constexpr int MAC_THREADS = 128;
 constexpr int MAC_BINS = MAC_THREADS / 2;          // bins per CTA of conv_mac_kernel
 
+// 8-byte asynchronous copy global -> shared; nbytes = 0 writes zeros without touching src (LDGSTS with zero fill)
+__device__ __forceinline__ void cp_async8(void* dst_smem, const void* src, int nbytes) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(nbytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int MAC_STAGES = 2;          // rounds staged in shared memory: the one being consumed + one in flight
+constexpr size_t MAC_SMEM = sizeof(float2) * MAC_STAGES * MAC_NPT * MAC_THREADS;
+
 // One round of the walk = MAC_NPT consecutive blocks i0 .. i0+MAC_NPT-1.  prev / cur hold this lane's input spectra of the
-// previous / current round (cur[u] = X[i0 + u - jb]), so output u needs cur[u], cur[u-1], .., cur[0], prev[NPT-1], .., prev[u+1]
-// -- all static register indices; nxt receives the round after this one while the FMAs run.
-__device__ __forceinline__ void mac_round(const float2 (&prev)[MAC_NPT], const float2 (&cur)[MAC_NPT], float2 (&nxt)[MAC_NPT],
-                                          const float2 (&h)[MAC_NPT], const float2* __restrict__ xs, float* __restrict__ yf,
-                                          int i0, int jb, int nblk, int s, int accumulate) {
+// previous / current round (cur[u] = X[i0 + u - jb], read from the thread's own staging slots), so output u needs cur[u],
+// cur[u-1], .., cur[0], prev[NPT-1], .., prev[u+1] -- all static register indices.
+__device__ __forceinline__ void mac_round(const float2 (&prev)[MAC_NPT], float2 (&cur)[MAC_NPT], const float2 (&h)[MAC_NPT],
+                                          const float2* __restrict__ slot, float* __restrict__ yf, int i0, int nblk, int s,
+                                          int accumulate) {
 #pragma unroll
-    for (int u = 0; u < MAC_NPT; ++u) {
-        const int in = i0 + MAC_NPT + u, ix = in - jb;
-        nxt[u] = (in < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
-    }
+    for (int u = 0; u < MAC_NPT; ++u) cur[u] = slot[u * MAC_THREADS];
 #pragma unroll
     for (int u = 0; u < MAC_NPT; ++u) {
         const int i = i0 + u;                          // warp-uniform
@@ -184,30 +192,51 @@ __device__ __forceinline__ void mac_round(const float2 (&prev)[MAC_NPT], const f
     }
 }
 
-__global__ void __launch_bounds__(MAC_THREADS, 4) conv_mac_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
+__global__ void __launch_bounds__(MAC_THREADS, 5) conv_mac_kernel(const float2* __restrict__ S, const float2* __restrict__ Hf,
                                                                   float2* __restrict__ Y, int nblk, int np, int jg, int accumulate) {
+    extern __shared__ __align__(16) float2 mac_sm[];   // [MAC_STAGES][MAC_NPT][MAC_THREADS]
     const int s = threadIdx.x & 1;
     const int k = blockIdx.x * MAC_BINS + (threadIdx.x >> 1), b2 = blockIdx.y;
     const int jb = jg + s * MAC_NPT;               // first partition of this lane
-    float2 h[MAC_NPT], ra[MAC_NPT], rb[MAC_NPT], rc[MAC_NPT];
     const float2* xs = S + (size_t)b2 * nblk * CONV_N2 + k;
     float* yf = reinterpret_cast<float*>(Y + (size_t)b2 * nblk * CONV_N2 + k) + s;
+    float2* mine = mac_sm + threadIdx.x;
+    const int R = (nblk - jg + MAC_NPT - 1) / MAC_NPT;
+
+    // the next round's spectra travel through the thread's own shared-memory slots (cp.async, zero fill at the edges) while
+    // the current round is multiplied: no registers and no barrier for the loads in flight.  History: loads issued and
+    // consumed in the same step 0.36 ms; register look-ahead with three rotating sets 0.265 ms (128 registers, 4 CTAs/SM)
+    auto issue = [&](int r) {
+        if (r < R) {
+            const int i0 = jg + r * MAC_NPT;
+            const float2* xr = xs + (long long)(i0 - jb) * CONV_N2;      // a zero-byte copy never reads its source
+            float2* slot = mine + (size_t)(r % MAC_STAGES) * (MAC_NPT * MAC_THREADS);
+#pragma unroll
+            for (int u = 0; u < MAC_NPT; ++u) {
+                const int in = i0 + u;
+                cp_async8(slot + u * MAC_THREADS, xr + (size_t)u * CONV_N2, (in < nblk && in >= jb) ? 8 : 0);
+            }
+        }
+        cp_async_commit();
+    };
+    issue(0);
+    float2 h[MAC_NPT], ra[MAC_NPT], rb[MAC_NPT];
 #pragma unroll
     for (int j = 0; j < MAC_NPT; ++j) {
         h[j] = (jb + j < np) ? Hf[(size_t)(jb + j) * CONV_N2 + k] : make_float2(0.f, 0.f);
-        ra[j] = make_float2(0.f, 0.f);
-        const int ix = jg + j - jb;                // the first round's spectra
-        rb[j] = (jg + j < nblk && ix >= 0) ? xs[(size_t)ix * CONV_N2] : make_float2(0.f, 0.f);
+        ra[j] = rb[j] = make_float2(0.f, 0.f);
     }
-    // software pipeline over rounds with the three register sets taking turns as previous / current / incoming spectra (no
-    // copies); with the loads issued and consumed in the same step the kernel sat at 2.1 TB/s whatever its arithmetic looked like
-    for (int i0 = jg; i0 < nblk; i0 += 3 * MAC_NPT) {
-        mac_round(ra, rb, rc, h, xs, yf, i0, jb, nblk, s, accumulate);
-        if (i0 + MAC_NPT >= nblk) break;
-        mac_round(rb, rc, ra, h, xs, yf, i0 + MAC_NPT, jb, nblk, s, accumulate);
-        if (i0 + 2 * MAC_NPT >= nblk) break;
-        mac_round(rc, ra, rb, h, xs, yf, i0 + 2 * MAC_NPT, jb, nblk, s, accumulate);
+    for (int r = 0; r < R; r += 2) {
+        issue(r + 1);
+        cp_async_wait<MAC_STAGES - 1>();
+        mac_round(ra, rb, h, mine + (size_t)(r % MAC_STAGES) * (MAC_NPT * MAC_THREADS), yf, jg + r * MAC_NPT, nblk, s, accumulate);
+        if (r + 1 >= R) break;
+        issue(r + 2);
+        cp_async_wait<MAC_STAGES - 1>();
+        mac_round(rb, ra, h, mine + (size_t)((r + 1) % MAC_STAGES) * (MAC_NPT * MAC_THREADS), yf, jg + (r + 1) * MAC_NPT, nblk, s,
+                  accumulate);
     }
+    cp_async_wait<0>();
 }
 
 // y block i of voice pair b2 = last P samples of IFFT(Y[b2,i]) / 4096
@@ -241,14 +270,6 @@ __global__ void __launch_bounds__(CONV_THREADS) conv_ifft_kernel(const float2* _
 // spectra of the next round are requested a round ahead.  Chunk partials are summed in a fixed order by the finish kernel.
 // ------------------------------------------------------------------------------------------------
 constexpr int GIR_NPT = GIR_NP / 2;
-
-// 8-byte asynchronous copy global -> shared; nbytes = 0 writes zeros without touching src (LDGSTS with zero fill)
-__device__ __forceinline__ void cp_async8(void* dst_smem, const void* src, int nbytes) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(nbytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 constexpr int GIR_STAGES = 2;          // rounds staged in shared memory: the one being consumed + one in flight (48 KB: 4 CTAs per SM)
 constexpr size_t GIR_SMEM = sizeof(float2) * GIR_STAGES * 2 * GIR_NPT * MAC_THREADS;
@@ -469,7 +490,7 @@ extern "C" int ddsp_conv_forward(const float* x, const float* ir, float* y, void
     DDSP_CHECK_LAUNCH("conv_spectra_kernel(x)");
     float2* S1 = reinterpret_cast<float2*>(base + p.off_S1);
     for (int jg = 0; jg < p.np; jg += MAC_NP) {
-        conv_mac_kernel<<<dim3(CONV_N2 / MAC_BINS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+        conv_mac_kernel<<<dim3(CONV_N2 / MAC_BINS, p.B2), MAC_THREADS, MAC_SMEM, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
         DDSP_CHECK_LAUNCH("conv_mac_kernel");
     }
     conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, y, B, N, p.nblk, 0);
@@ -518,7 +539,7 @@ extern "C" int ddsp_conv_backward(const float* g, const float* x, const float* i
         conv_spectra_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(g, S0, B, N, p.nblk, 3, 1, 0);
         DDSP_CHECK_LAUNCH("conv_spectra_kernel(flip g)");
         for (int jg = 0; jg < p.np; jg += MAC_NP) {
-            conv_mac_kernel<<<dim3(CONV_N2 / MAC_BINS, p.B2), MAC_THREADS, 0, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
+            conv_mac_kernel<<<dim3(CONV_N2 / MAC_BINS, p.B2), MAC_THREADS, MAC_SMEM, st>>>(S0, Hf, S1, p.nblk, p.np, jg, jg > 0);
             DDSP_CHECK_LAUNCH("conv_mac_kernel(gx)");
         }
         conv_ifft_kernel<<<dim3(p.nblk, p.B2), CONV_THREADS, smem, st>>>(S1, gx, B, N, p.nblk, 1);
