@@ -120,18 +120,30 @@ __global__ void __launch_bounds__(CONV_THREADS, 3) conv_spectra_kernel(const flo
     const float* xb = v1 < B ? x + (size_t)v1 * N : nullptr;
     const long long base = (long long)(i + blk_shift - 1) * CONV_P;
     float2 v[8];
+    if (base >= 0 && base + CONV_N2 <= N) {
+        // segment entirely inside the signal (all but the first and last block): plain strided loads, q < 4 is the first half
+        const float* pa = reverse ? xa + (N - 1 - base) - tid : xa + base + tid;
+        const float* pb = xb ? (reverse ? xb + (N - 1 - base) - tid : xb + base + tid) : nullptr;
+        const int step = reverse ? -CONV_THREADS : CONV_THREADS;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-        const int m = tid + q * CONV_THREADS;
-        const bool on = (m < CONV_P) ? (halves & 1) : (halves & 2);
-        const long long n = base + m;
-        float re = 0.f, im = 0.f;
-        if (on && n >= 0 && n < N) {
-            const long long idx = reverse ? (N - 1 - n) : n;
-            re = xa[idx];
-            if (xb) im = xb[idx];
+        for (int q = 0; q < 8; ++q) {
+            const bool on = (q < 4) ? (halves & 1) : (halves & 2);
+            v[q] = on ? make_float2(pa[q * step], pb ? pb[q * step] : 0.f) : make_float2(0.f, 0.f);
         }
-        v[q] = make_float2(re, im);
+    } else {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int m = tid + q * CONV_THREADS;
+            const bool on = (m < CONV_P) ? (halves & 1) : (halves & 2);
+            const long long n = base + m;
+            float re = 0.f, im = 0.f;
+            if (on && n >= 0 && n < N) {
+                const long long idx = reverse ? (N - 1 - n) : n;
+                re = xa[idx];
+                if (xb) im = xb[idx];
+            }
+            v[q] = make_float2(re, im);
+        }
     }
     fft8_group<CONV_N2, float, false>(v, fsm, tid);
     float2* dst = S + ((size_t)b2 * nblk + i) * CONV_N2;
