@@ -176,26 +176,30 @@ constexpr size_t MAC_SMEM = sizeof(float2) * MAC_STAGES * MAC_NPT * MAC_THREADS;
 // One round of the walk = MAC_NPT consecutive blocks i0 .. i0+MAC_NPT-1.  prev / cur hold this lane's input spectra of the
 // previous / current round (cur[u] = X[i0 + u - jb], read from the thread's own staging slots), so output u needs cur[u],
 // cur[u-1], .., cur[0], prev[NPT-1], .., prev[u+1] -- all static register indices.
-__device__ __forceinline__ void mac_round(const float2 (&prev)[MAC_NPT], float2 (&cur)[MAC_NPT], const float2 (&h)[MAC_NPT],
-                                          const float2* __restrict__ slot, float* __restrict__ yf, int i0, int nblk, int s,
-                                          int accumulate) {
+// Packed arithmetic: with x = (xr, xi) as it lies in its register pair, A += x * (hr, hr) and B += x * (hi, hi) are one
+// FFMA2 each and the product is (A.x - B.y, A.y + B.x): two issue slots per complex multiply-add instead of four (the FMA
+// pipe does the same work either way; the kernel was issue-bound at 81 % of its slots with 58 % of the pipe).
+__device__ __forceinline__ void mac_round(const float2 (&prev)[MAC_NPT], float2 (&cur)[MAC_NPT], const float2 (&hrr)[MAC_NPT],
+                                          const float2 (&hii)[MAC_NPT], const float2* __restrict__ slot, float* __restrict__ yf,
+                                          int i0, int nblk, int s, int accumulate) {
 #pragma unroll
     for (int u = 0; u < MAC_NPT; ++u) cur[u] = slot[u * MAC_THREADS];
 #pragma unroll
     for (int u = 0; u < MAC_NPT; ++u) {
         const int i = i0 + u;                          // warp-uniform
         if (i < nblk) {
-            float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);          // four independent FMA chains
+            float2 A0 = make_float2(0.f, 0.f), A1 = A0, B0 = A0, B1 = A0;           // four independent packed chains
 #pragma unroll
-            for (int j = 0; j < MAC_NPT; ++j) {
-                const float2 xv = (u - j >= 0) ? cur[(u - j + MAC_NPT) % MAC_NPT] : prev[(u - j + MAC_NPT) % MAC_NPT], hv = h[j];
-                a0.x = fmaf(xv.x, hv.x, a0.x);
-                a1.x = fmaf(-xv.y, hv.y, a1.x);
-                a0.y = fmaf(xv.x, hv.y, a0.y);
-                a1.y = fmaf(xv.y, hv.x, a1.y);
+            for (int j = 0; j < MAC_NPT; j += 2) {
+                const float2 x0 = (u - j >= 0) ? cur[(u - j + MAC_NPT) % MAC_NPT] : prev[(u - j + MAC_NPT) % MAC_NPT];
+                const float2 x1 = (u - j - 1 >= 0) ? cur[(u - j - 1 + MAC_NPT) % MAC_NPT] : prev[(u - j - 1 + MAC_NPT) % MAC_NPT];
+                A0 = __ffma2_rn(x0, hrr[j], A0);
+                B0 = __ffma2_rn(x0, hii[j], B0);
+                A1 = __ffma2_rn(x1, hrr[j + 1], A1);
+                B1 = __ffma2_rn(x1, hii[j + 1], B1);
             }
             // lane s keeps component s of the sum over both lanes' partitions and stores that float: no divergent store
-            const float re = a0.x + a1.x, im = a0.y + a1.y;
+            const float re = (A0.x + A1.x) - (B0.y + B1.y), im = (A0.y + A1.y) + (B0.x + B1.x);
             float mine = (s ? im : re) + __shfl_xor_sync(0xffffffffu, s ? re : im, 1);
             float* dst = yf + (size_t)i * (2 * CONV_N2);
             if (accumulate) mine += *dst;
@@ -232,20 +236,22 @@ __global__ void __launch_bounds__(MAC_THREADS, 5) conv_mac_kernel(const float2* 
         cp_async_commit();
     };
     issue(0);
-    float2 h[MAC_NPT], ra[MAC_NPT], rb[MAC_NPT];
+    float2 hrr[MAC_NPT], hii[MAC_NPT], ra[MAC_NPT], rb[MAC_NPT];
 #pragma unroll
     for (int j = 0; j < MAC_NPT; ++j) {
-        h[j] = (jb + j < np) ? Hf[(size_t)(jb + j) * CONV_N2 + k] : make_float2(0.f, 0.f);
+        const float2 h = (jb + j < np) ? Hf[(size_t)(jb + j) * CONV_N2 + k] : make_float2(0.f, 0.f);
+        hrr[j] = make_float2(h.x, h.x);
+        hii[j] = make_float2(h.y, h.y);
         ra[j] = rb[j] = make_float2(0.f, 0.f);
     }
     for (int r = 0; r < R; r += 2) {
         issue(r + 1);
         cp_async_wait<MAC_STAGES - 1>();
-        mac_round(ra, rb, h, mine + (size_t)(r % MAC_STAGES) * (MAC_NPT * MAC_THREADS), yf, jg + r * MAC_NPT, nblk, s, accumulate);
+        mac_round(ra, rb, hrr, hii, mine + (size_t)(r % MAC_STAGES) * (MAC_NPT * MAC_THREADS), yf, jg + r * MAC_NPT, nblk, s, accumulate);
         if (r + 1 >= R) break;
         issue(r + 2);
         cp_async_wait<MAC_STAGES - 1>();
-        mac_round(rb, ra, h, mine + (size_t)((r + 1) % MAC_STAGES) * (MAC_NPT * MAC_THREADS), yf, jg + (r + 1) * MAC_NPT, nblk, s,
+        mac_round(rb, ra, hrr, hii, mine + (size_t)((r + 1) % MAC_STAGES) * (MAC_NPT * MAC_THREADS), yf, jg + (r + 1) * MAC_NPT, nblk, s,
                   accumulate);
     }
     cp_async_wait<0>();
@@ -288,8 +294,10 @@ constexpr size_t GIR_SMEM = sizeof(float2) * GIR_STAGES * 2 * GIR_NPT * MAC_THRE
 
 // One round: cur[u] = X[i0 + u - jb] and g[u] = G[i0 + u] come out of the thread's own staging slots;
 // acc[j] += g[u] * conj(X[i0 + u - jb - j]) with X[.. < round start] in prev (the previous round's cur).
-__device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], float2 (&cur)[GIR_NPT], float2 (&acc)[GIR_NPT],
-                                          const float2* __restrict__ slot) {
+// Packed: with x = (xr, xi) in its register pair, A[j] += (gx, gx) * x and B[j] += (gy, gy) * x are one FFMA2 each and
+// g * conj(x) accumulates as (A.x + B.y, B.x - A.y) -- combined once, at the end of the kernel.
+__device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], float2 (&cur)[GIR_NPT], float2 (&A)[GIR_NPT],
+                                          float2 (&Bc)[GIR_NPT], const float2* __restrict__ slot) {
     float2 g[GIR_NPT];
 #pragma unroll
     for (int u = 0; u < GIR_NPT; ++u) {
@@ -298,12 +306,12 @@ __device__ __forceinline__ void gir_round(const float2 (&prev)[GIR_NPT], float2 
     }
 #pragma unroll
     for (int u = 0; u < GIR_NPT; ++u) {
-        const float2 gv = g[u];                        // zero past the last block: nothing to guard
+        const float2 gxx = make_float2(g[u].x, g[u].x), gyy = make_float2(g[u].y, g[u].y);   // zero past the last block
 #pragma unroll
         for (int j = 0; j < GIR_NPT; ++j) {
             const float2 xv = (u - j >= 0) ? cur[(u - j + GIR_NPT) % GIR_NPT] : prev[(u - j + GIR_NPT) % GIR_NPT];
-            acc[j].x = fmaf(gv.x, xv.x, fmaf(gv.y, xv.y, acc[j].x));
-            acc[j].y = fmaf(gv.y, xv.x, fmaf(-gv.x, xv.y, acc[j].y));
+            A[j] = __ffma2_rn(gxx, xv, A[j]);
+            Bc[j] = __ffma2_rn(gyy, xv, Bc[j]);
         }
     }
 }
@@ -345,9 +353,9 @@ __global__ void __launch_bounds__(MAC_THREADS, 4) conv_gir_kernel(const float2* 
         cp_async_commit();
     };
 
-    float2 acc[GIR_NPT], ra[GIR_NPT], rb[GIR_NPT];
+    float2 accA[GIR_NPT], accB[GIR_NPT], ra[GIR_NPT], rb[GIR_NPT];
 #pragma unroll
-    for (int j = 0; j < GIR_NPT; ++j) acc[j] = ra[j] = rb[j] = make_float2(0.f, 0.f);
+    for (int j = 0; j < GIR_NPT; ++j) accA[j] = accB[j] = ra[j] = rb[j] = make_float2(0.f, 0.f);
 #pragma unroll
     for (int r = 0; r < GIR_STAGES - 1; ++r) issue(r);
     for (int r = 0; r < R; r += 2) {
@@ -358,7 +366,7 @@ __global__ void __launch_bounds__(MAC_THREADS, 4) conv_gir_kernel(const float2* 
 #pragma unroll
             for (int j = 0; j < GIR_NPT; ++j) ra[j] = make_float2(0.f, 0.f);      // a new voice pair starts with an empty history
         }
-        gir_round(ra, rb, acc, mine + (size_t)(r % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS));
+        gir_round(ra, rb, accA, accB, mine + (size_t)(r % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS));
         if (r + 1 >= R) break;
         issue(r + GIR_STAGES);
         cp_async_wait<GIR_STAGES - 1>();
@@ -366,12 +374,12 @@ __global__ void __launch_bounds__(MAC_THREADS, 4) conv_gir_kernel(const float2* 
 #pragma unroll
             for (int j = 0; j < GIR_NPT; ++j) rb[j] = make_float2(0.f, 0.f);
         }
-        gir_round(rb, ra, acc, mine + (size_t)((r + 1) % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS));
+        gir_round(rb, ra, accA, accB, mine + (size_t)((r + 1) % GIR_STAGES) * (2 * GIR_NPT * MAC_THREADS));
     }
     cp_async_wait<0>();
 #pragma unroll
     for (int j = 0; j < GIR_NPT; ++j)
-        if (jb + j < np) part[((size_t)c * np + jb + j) * CONV_N2 + k] = acc[j];
+        if (jb + j < np) part[((size_t)c * np + jb + j) * CONV_N2 + k] = make_float2(accA[j].x + accB[j].y, accB[j].x - accA[j].y);
 }
 
 __global__ void __launch_bounds__(CONV_THREADS) conv_gir_finish_kernel(const float2* __restrict__ part, float* __restrict__ gir,
