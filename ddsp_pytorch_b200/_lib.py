@@ -24,6 +24,8 @@ SIGNATURES = {
     "ddsp_osc_backward_scratch_bytes": (_sz, [_i, _i, _i]),
     "ddsp_osc_backward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ddsp_osc_live": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ddsp_rescale_forward": (_i, [_p, _p, _i, _i, _i, _i, _p]),
+    "ddsp_rescale_backward": (_i, [_p, _p, _i, _i, _i, _i, _p]),
     "ddsp_noise_forward": (_i, [_p, _p, _p, _i, _u64, _u32, _p, _u32, _i, _i, _i, _i, _p]),
     "ddsp_noise_backward": (_i, [_p, _p, _p, _u64, _u32, _p, _u32, _i, _i, _i, _i, _p]),
     "ddsp_noise_uniform": (_i, [_p, _u64, _u32, _u32, _i, _i, _i, _p]),

@@ -26,6 +26,32 @@ class OscillatorBank(nn.Module):
             raise RuntimeError(f"OscillatorBank: x['c'] has {c.shape[-1]} harmonics, module has {self.n_harmonics}")
         return ops.oscillator_bank(x["f0"], c, x["a"], self.sample_rate, self.hop_size)
 
+    # ---- the reference's public helper methods (harmonic_oscillator.py:24-55; no caller outside the class) -------------
+    # forward() above does NOT go through them -- the kernels never build a [B,N,K] tensor.  They are kept for code that
+    # inspects the intermediate quantities, stated op for op as the reference states them on top of ops.rescale, so they
+    # materialise what the reference materialises and carry the reference's own fp32 phase drift (SURVEY F5).
+    def rescale(self, x):
+        """[B,T,C] -> [B,T*hop,C]  (:52-55)."""
+        return ops.rescale(x, self.hop_size)
+
+    def prepare_harmonics(self, f0, harm_amps):
+        """(:24-37) -> (radians per sample of every harmonic, upsampled [B,N,K]; Nyquist-masked, normalised amplitudes [B,T,K])."""
+        harmonics = self.harmonics.to(f0.device).view(1, 1, -1) * f0              # int64 x fp32 -> fp32 Hz (:26-29)
+        mask = harmonics > self.sample_rate // 2                                   # (:31)
+        harm_amps = harm_amps.masked_fill(mask, 0.)
+        harm_amps = harm_amps / harm_amps.sum(-1, keepdim=True)                    # (:33), out of place: the caller's tensor is kept
+        harmonics = harmonics * (2 * torch.pi) / self.sample_rate                  # (:34-35)
+        return self.rescale(harmonics), harm_amps
+
+    @staticmethod
+    def generate_phases(harmonics):
+        """(:39-43) cumulative sum over samples, wrapped to [0, 2 pi)."""
+        return torch.cumsum(harmonics, dim=1) % (2 * torch.pi)
+
+    def generate_signal(self, harm_amps, loudness, phases):
+        """(:45-50) sum_k a_up * c_up[k] * sin(phase[k])."""
+        return torch.sum(self.rescale(loudness) * self.rescale(harm_amps) * torch.sin(phases), dim=2)
+
 
 class FilteredNoise(nn.Module):
     """Drop-in for model/ddsp/filtered_noise.py:35-53.

@@ -364,6 +364,36 @@ def mss_loss(x_pred, x_true, n_ffts, alpha: float = 1.0, overlap: float = 0.75, 
     return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps), tuple(windows))
 
 
+class _Rescale(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, hop: int):
+        x_ = _f32(x)
+        if x_.dim() != 3:
+            raise RuntimeError(f"rescale: expected [B,T,C], got {tuple(x.shape)}")
+        B, T, C = x_.shape
+        y = torch.empty(B, T * hop, C, dtype=torch.float32, device=x_.device)
+        with torch.cuda.device(x_.device):
+            _lib.call("ddsp_rescale_forward", x_.data_ptr(), y.data_ptr(), B, T, C, hop, _stream())
+        ctx.dims = (B, T, C, hop, x.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        B, T, C, hop, dtype = ctx.dims
+        g_ = _f32(g)
+        gx = torch.empty(B, T, C, dtype=torch.float32, device=g_.device)
+        with torch.cuda.device(g_.device):
+            _lib.call("ddsp_rescale_backward", g_.data_ptr(), gx.data_ptr(), B, T, C, hop, _stream())
+        return gx.to(dtype), None
+
+
+def rescale(x: torch.Tensor, hop: int) -> torch.Tensor:
+    """[B,T,C] -> [B,T*hop,C]: ``OscillatorBank.rescale`` (harmonic_oscillator.py:52-55), linear upsampling with half-pixel
+    centres.  Not used by the synthesis ops (they fold the interpolation into their kernels); it backs the reference's
+    public helper methods."""
+    return _Rescale.apply(x, int(hop))
+
+
 def oscillator_live(f0, c, a, last_phases, sample_rate: int, hop: int):
     """OscillatorBank.live (harmonic_oscillator.py:64-75), no gradient: returns (audio [B,T*hop], new last_phases [K] fp32)."""
     f0_, c_, a_ = _f32(f0), _f32(c), _f32(a)

@@ -80,6 +80,13 @@ int ddsp_osc_live(const float* f0, const float* c, const float* a, const float* 
                   float* last_out, float* y, void* state, int B, int T, int K, int hop,
                   int sample_rate, void* stream);
 
+/* OscillatorBank.rescale, harmonic_oscillator.py:52-55 (F.interpolate(..., scale_factor=hop, mode='linear'), half-pixel
+ * centres): x [B,T,C] -> y [B,T*hop,C].  The synthesis entry points above never build this tensor; it backs the
+ * reference's public helper methods (prepare_harmonics :24-37, generate_signal :45-50), which the drop-in keeps.
+ * backward: gx [B,T,C] = adjoint applied to gy [B,T*hop,C] (fixed summation order). */
+int ddsp_rescale_forward(const float* x, float* y, int B, int T, int C, int hop, void* stream);
+int ddsp_rescale_backward(const float* gy, float* gx, int B, int T, int C, int hop, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Filtered noise  --  FilteredNoise.forward, filtered_noise.py:40-53
  *   (amp_to_impulse_response :7-22, fft_convolve :25-32; per frame, tails dropped, no overlap-add)

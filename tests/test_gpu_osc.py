@@ -130,3 +130,51 @@ def test_live_blocks_against_oracle(hop, K, sr):
         assert float((got.double().cpu() - want).abs().max()) <= WAVE_TOL
         dphi = (bank.last_phases.double().cpu() - last).abs()
         assert float(torch.minimum(dphi, 2 * np.pi - dphi).max()) <= 1e-4
+
+
+@pytest.mark.parametrize("B,T,C,hop", [(2, 5, 3, 8), (1, 1, 4, 16), (3, 7, 1, 5), (2, 9, 33, 512), (1, 4, 2, 1)])
+def test_rescale_forward_and_adjoint(B, T, C, hop):
+    """OscillatorBank.rescale (harmonic_oscillator.py:52-55) through ddsp_rescale_forward/backward against the oracle's
+    F.interpolate restatement in fp64 and against its index-arithmetic form; the backward is the exact adjoint."""
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(B * 100 + T * 10 + hop)
+    x = torch.randn(B, T, C, generator=gen)
+    g = torch.randn(B, T * hop, C, generator=gen)
+    xd = x.double().requires_grad_(True)
+    want = O.upsample_linear(xd, hop)
+    (want * g.double()).sum().backward()
+    xc = x.cuda().requires_grad_(True)
+    got = ops.rescale(xc, hop)
+    (got * g.cuda()).sum().backward()
+    assert got.shape == (B, T * hop, C)
+    assert float((got.detach().double().cpu() - want.detach()).abs().max()) <= 2e-6 * float(want.detach().abs().max())
+    assert float((got.detach().double().cpu() - O.upsample_linear_explicit(x.double(), hop)).abs().max()) <= 2e-6 * float(x.abs().max())
+    assert float((xc.grad.double().cpu() - xd.grad).abs().max()) <= 1e-5 * float(xd.grad.abs().max())
+
+
+def test_public_helper_methods_follow_the_reference():
+    """prepare_harmonics / generate_phases / generate_signal / rescale (harmonic_oscillator.py:24-55) are kept on the drop-in:
+    chained as the reference's forward chains them they reproduce the oracle's fp32 restatement and agree with the kernel
+    forward (which never builds these tensors) to the fp32 reference's own accuracy on a short clip."""
+    import ddsp_pytorch_b200 as d
+    from oracle import ddsp_oracle as O
+    conf = d.Config(sample_rate=16000, hop_length=64, n_harmonics=40, n_noise_filters=65)
+    B, T, K, hop, sr = 2, 6, 40, 64, 16000
+    f0, c, a, _ = O.synthetic_controls(B, T, K, 65, sr, hop, seed=3)
+    bank = d.OscillatorBank(conf).cuda()
+    f0c, cc, ac = f0.cuda(), c.cuda(), a.cuda()
+    c_before = cc.clone()
+    harm, amps = bank.prepare_harmonics(f0c, cc)
+    assert torch.equal(cc, c_before)                                   # the reference does not mutate x['c'] either
+    w_harm, w_amps = O.osc_prepare(f0.double(), c.double(), K, sr, hop)
+    assert harm.shape == (B, T * hop, K) and amps.shape == (B, T, K)
+    assert float((harm.double().cpu() - w_harm).abs().max()) <= 1e-6 * float(w_harm.abs().max())
+    assert float((amps.double().cpu() - w_amps).abs().max()) <= 1e-6
+    phases = d.OscillatorBank.generate_phases(harm)
+    assert float(phases.min()) >= 0.0 and float(phases.max()) < 2 * np.pi + 1e-5
+    y = bank.generate_signal(amps, ac, phases)
+    want = O.oscillator_bank(f0.double(), c.double(), a.double(), K, sr, hop)
+    assert float((y.double().cpu() - want).abs().max()) <= 1e-3       # fp32 cumsum drift of the reference's own formulation
+    y_kernel = bank({"f0": f0c, "c": cc, "a": ac})
+    assert float((y_kernel.double().cpu() - want).abs().max()) <= WAVE_TOL
