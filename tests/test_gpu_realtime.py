@@ -67,3 +67,40 @@ def test_graph_replay_continues_the_eager_stream():
     assert float(eager.abs().max()) > 1e-3
     assert float((eager - graphed).abs().max()) <= 1e-6 * float(eager.abs().max())
     assert not torch.equal(graphed[3], graphed[4])            # state and noise advance between replays
+
+
+def test_live_path_from_a_callback_thread():
+    """rt/synth.py:40-55 calls the decoder from the JACK process-callback thread while the main thread waits (SURVEY 8b,
+    threading row): the live ops keep no thread-affine state -- blocks alternated between a worker thread and the main
+    thread continue one stream, bit for bit, with a twin that stays on the main thread."""
+    import threading
+    import ddsp_pytorch_b200 as d
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
+    conf = d.Config(sample_rate=4000, hop_length=64, n_harmonics=20, n_noise_filters=9)
+    torch.manual_seed(5)
+    mods = []
+    for _ in range(2):
+        torch.manual_seed(5)
+        mods.append((d.OscillatorBank(conf).cuda(), d.FilteredNoise(conf, seed=11), d.Reverb(conf, initial_wet=1.0).cuda()))
+    mods[1][2].load_state_dict(mods[0][2].state_dict())
+
+    def block(m, blk):
+        f0, c, a, H = (t.cuda() for t in synthetic_controls(1, 4, conf.n_harmonics, conf.n_noise_filters, conf.sample_rate,
+                                                            conf.hop_length, seed=40 + blk))
+        bank, fn, rv = m
+        with torch.no_grad():
+            y = rv.live_forward(bank.live({"f0": f0, "c": c, "a": a}) + fn({"H": H}))
+        return y.cpu()
+
+    for blk in range(4):
+        want = block(mods[0], blk)
+        if blk % 2 == 0:
+            box = {}
+            th = threading.Thread(target=lambda: box.update(y=block(mods[1], blk)))
+            th.start()
+            th.join()
+            got = box["y"]
+        else:
+            got = block(mods[1], blk)
+        assert got.shape == (1, 4 * conf.hop_length)
+        assert torch.equal(got, want), f"block {blk} differs between threads"
