@@ -630,10 +630,17 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
     if (live) {
         const float* gf = g + frame * hop;
         const float* nf = noise ? noise + frame * hop : nullptr;
-        for (int q = l; q < (hop >> 2); q += TS) {
-            *reinterpret_cast<float4*>(gs + 4 * q) = *reinterpret_cast<const float4*>(gf + 4 * q);
+        // the frame's gradient is requested first (hop/4 float4 over hop/16 lanes: always 4 per lane) and parked in registers
+        // while the noise is generated; copied load-by-load inside the loop it cost 13.6 % of the warp samples (ncu r01g)
+        float4 gq[4];
+#pragma unroll
+        for (int it = 0; it < 4; ++it) gq[it] = *reinterpret_cast<const float4*>(gf + 4 * (l + it * TS));
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int q = l + it * TS;
             const float4 v = nf ? *reinterpret_cast<const float4*>(nf + 4 * q)
                                 : philox_noise4((uint32_t)q, t, voice_offset + b, offset, key);
+            *reinterpret_cast<float4*>(gs + 4 * q) = gq[it];
             *reinterpret_cast<float4*>(u + swz(PADL + 4 * q)) = v;
             if (4 * q < half) {
                 const float vv[4] = {v.x, v.y, v.z, v.w};
