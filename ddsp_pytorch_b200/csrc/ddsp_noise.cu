@@ -436,7 +436,18 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
     const int half = L.half, TP = L.TP, PADL = L.PADL;
     const long long frame = (long long)blockIdx.x * FPB + team;
     const bool live = frame < frames;
-    const uint32_t b = live ? (uint32_t)(frame / T) : 0u, t = live ? (uint32_t)(frame % T) : 0u;
+    // (voice, frame-in-voice) of this team's frame: a 32-bit division when the frame index fits (it does unless B*T >= 2^32);
+    // the 64-bit one is a ~100-instruction dependent sequence in front of the first Philox counter
+    uint32_t b = 0u, t = 0u;
+    if (live) {
+        if (frame <= 0xffffffffLL) {
+            b = (uint32_t)frame / (uint32_t)T;
+            t = (uint32_t)frame - b * (uint32_t)T;
+        } else {
+            b = (uint32_t)(frame / T);
+            t = (uint32_t)(frame % T);
+        }
+    }
 
     // ---- stage 1: H, noise (generated or read), zero pads -----------------------------------------
     // The frame's magnitudes are requested first and parked in registers while the noise is generated (as the gradient is in
@@ -642,7 +653,18 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
     const int half = L.half, PADL = L.PADL, nsl = L.nsl, ntg = L.ntg;
     const long long frame = (long long)blockIdx.x * FPB + team;
     const bool live = frame < frames;
-    const uint32_t b = live ? (uint32_t)(frame / T) : 0u, t = live ? (uint32_t)(frame % T) : 0u;
+    // (voice, frame-in-voice) of this team's frame: a 32-bit division when the frame index fits (it does unless B*T >= 2^32);
+    // the 64-bit one is a ~100-instruction dependent sequence in front of the first Philox counter
+    uint32_t b = 0u, t = 0u;
+    if (live) {
+        if (frame <= 0xffffffffLL) {
+            b = (uint32_t)frame / (uint32_t)T;
+            t = (uint32_t)frame - b * (uint32_t)T;
+        } else {
+            b = (uint32_t)(frame / T);
+            t = (uint32_t)(frame % T);
+        }
+    }
     const int jw = hop - half;
 
     for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
