@@ -219,3 +219,27 @@ def test_whole_path_golden(golden):
         assert l2rel(got, g[key]) <= 2e-4, key
     assert abs(float(rv.decay.grad) - float(g["g_rev_decay"])) <= 2e-4 * abs(float(g["g_rev_decay"]))
     assert abs(float(rv.wet.grad) - float(g["g_rev_wet"])) <= 2e-4 * abs(float(g["g_rev_wet"]))
+
+
+def test_mss_gradient_exceedances_are_sign_ties():
+    """The two L1 terms put a sign() into d loss / d S_pred.  A bin whose predicted and true power agree to ~1e-6 relative makes
+    that sign -- and one windowed sinusoid of the gradient -- arbitrary in fp32, for this kernel and for the reference's own fp32
+    run alike (about one random input in 600 at this shape; found by scratch/fuzz.py, settled by scratch/mss_ties.py).  Every
+    case over the 1e-4 bound must be explained by such a tie; anything else is a defect."""
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(12345)
+    ffts, over = [512, 1024], 0
+    for it in range(250):
+        xp, xt = torch.randn(1, 4096, generator=gen) * 0.5, torch.randn(1, 4096, generator=gen) * 0.5
+        xpd = xp.double().requires_grad_(True)
+        O.mss_loss(xpd, xt.double(), ffts).backward()
+        xc = xp.cuda().requires_grad_(True)
+        ops.mss_loss(xc, xt.cuda(), ffts).backward()
+        err = float((xc.grad.double().cpu() - xpd.grad).abs().max() / xpd.grad.abs().max())
+        if err > 1e-4:
+            over += 1
+            gap = min(float(((O.power_spectrogram(xp.double(), n, n // 4) - O.power_spectrogram(xt.double(), n, n // 4)).abs()
+                             / O.power_spectrogram(xt.double(), n, n // 4)).min()) for n in ffts)
+            assert gap < 1e-5, f"case {it}: gradient error {err:.2e} without a tie (smallest relative gap {gap:.1e})"
+    assert over <= 3
