@@ -19,7 +19,7 @@ void set_error(const char* fmt, ...);
 
 #define DDSP_CHECK_LAUNCH(name)                                                          \
     do {                                                                                 \
-        cudaError_t e__ = cudaPeekAtLastError();                                         \
+        cudaError_t e__ = cudaGetLastError(); /* clears it: a failed launch must not poison later calls */ \
         if (e__ != cudaSuccess) {                                                        \
             ::ddsp::set_error("%s: launch failed: %s", name, cudaGetErrorString(e__));   \
             return 2;                                                                    \

@@ -59,6 +59,10 @@ static inline cudaError_t fft8_ensure_tables(cudaStream_t st) {
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     if (dev < 0 || dev >= 64 || !done[dev]) {
+        // first use on this device: the fill ends with a stream synchronise, which a capturing stream cannot take --
+        // the FFT-using entry points must run once outside CUDA-graph capture (torch's graph warm-up does that)
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(st, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone) return cudaErrorStreamCaptureUnsupported;
         fft8_init_tables_kernel<<<(9 * FFT8_SLOT + 255) / 256, 256, 0, st>>>();
         e = cudaStreamSynchronize(st);                  // one-time: later calls on other streams see the tables
         if (e == cudaSuccess && dev >= 0 && dev < 64) done[dev] = true;

@@ -24,6 +24,17 @@ def _bytes(n: int, device) -> torch.Tensor:
     return torch.empty(max(int(n), 1), dtype=torch.uint8, device=device)
 
 
+def _check_out(out: torch.Tensor, B: int, N: int, device, who: str) -> None:
+    """The fused-accumulate buffer is handed to the kernel as a raw pointer (float4 read-modify-write of B*N floats):
+    anything but a contiguous fp32 CUDA tensor of exactly that shape on the inputs' device would write out of bounds."""
+    if not isinstance(out, torch.Tensor) or not out.is_cuda or out.dtype != torch.float32 or not out.is_contiguous() \
+            or tuple(out.shape) != (B, N) or out.device != device:
+        desc = f"{tuple(out.shape)} {out.dtype} on {out.device}" if isinstance(out, torch.Tensor) else type(out).__name__
+        raise RuntimeError(f"{who}: out= must be a contiguous float32 CUDA tensor of shape ({B}, {N}) on {device}, got {desc}")
+    if out.data_ptr() % 16:
+        raise RuntimeError(f"{who}: out= must be 16-byte aligned (a view at an odd offset cannot take float4 stores)")
+
+
 class _Oscillator(torch.autograd.Function):
     @staticmethod
     def forward(ctx, f0, c, a, sample_rate: int, hop: int, out: Optional[torch.Tensor]):
@@ -33,9 +44,12 @@ class _Oscillator(torch.autograd.Function):
             raise RuntimeError(f"oscillator: f0 {tuple(f0.shape)} / a {tuple(a.shape)} do not match c {tuple(c.shape)}")
         dev = c_.device
         need_grad = c.requires_grad or a.requires_grad
+        accumulate = out is not None
+        if accumulate:
+            _check_out(out, B, T * hop, dev, "oscillator_bank")
+        ctx.saved_any = need_grad
         with torch.cuda.device(dev):
             lib = _lib.load()
-            accumulate = out is not None
             y = out if accumulate else torch.empty(B, T * hop, dtype=torch.float32, device=dev)
             z = torch.empty(B, T * hop, dtype=torch.float32, device=dev) if need_grad else None
             state = _bytes(lib.ddsp_osc_state_bytes(B, T, K), dev)
@@ -52,6 +66,9 @@ class _Oscillator(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, g):
+        g_out = g if ctx.needs_input_grad[5] else None
+        if not ctx.saved_any:                   # c and a are frozen; only an accumulated-into `out` carries a gradient
+            return None, None, None, None, None, g_out
         f0_, a_, z, state = ctx.saved_tensors
         B, T, K, hop, sample_rate = ctx.dims
         c_shape, a_shape, c_dtype, a_dtype = ctx.shapes
@@ -65,7 +82,6 @@ class _Oscillator(torch.autograd.Function):
             _lib.call("ddsp_osc_backward", g_.data_ptr(), f0_.data_ptr(), a_.data_ptr(), z.data_ptr(), state.data_ptr(),
                       scratch.data_ptr(), gc.data_ptr(), ga.data_ptr(), B, T, K, hop, sample_rate, _stream())
         # an accumulated-into `out` passes its gradient straight through to whoever produced it
-        g_out = g if ctx.needs_input_grad[5] else None
         return None, gc.view(c_shape).to(c_dtype), ga.view(a_shape).to(a_dtype), None, None, g_out
 
 
@@ -88,15 +104,19 @@ class _FilteredNoise(torch.autograd.Function):
             noise_ = _f32(noise)
             if noise_.numel() != B * T * hop:
                 raise RuntimeError(f"filtered_noise: noise {tuple(noise.shape)} is not [B,T,hop]=[{B},{T},{hop}]")
+        accumulate = out is not None
+        if accumulate:
+            _check_out(out, B, T * hop, dev, "filtered_noise")
         with torch.cuda.device(dev):
-            accumulate = out is not None
             y = out if accumulate else torch.empty(B, T * hop, dtype=torch.float32, device=dev)
             _lib.call("ddsp_noise_forward", H_.data_ptr(), noise_.data_ptr() if noise_ is not None else None, y.data_ptr(),
                       int(accumulate), seed, offset, offset_tensor.data_ptr() if offset_tensor is not None else None,
                       voice_offset, B, T, NB, hop, _stream())
         ctx.args = (B, T, NB, hop, seed, offset, voice_offset, H.shape, H.dtype)
         ctx.noise = noise_
-        ctx.offset_tensor = offset_tensor
+        # the device-side call counter may advance before backward runs (two forwards, one backward): keep the value this
+        # forward drew its Philox block with (a one-element clone is capturable in a CUDA graph)
+        ctx.offset_tensor = offset_tensor.clone() if (offset_tensor is not None and H.requires_grad) else None
         if accumulate:
             ctx.mark_dirty(out)
         return y
@@ -104,6 +124,9 @@ class _FilteredNoise(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         B, T, NB, hop, seed, offset, voice_offset, H_shape, H_dtype = ctx.args
+        g_out = g if ctx.needs_input_grad[6] else None
+        if not ctx.needs_input_grad[0]:
+            return None, None, None, None, None, None, g_out, None
         g_ = _f32(g)
         dev = g_.device
         with torch.cuda.device(dev):
@@ -111,7 +134,6 @@ class _FilteredNoise(torch.autograd.Function):
             _lib.call("ddsp_noise_backward", g_.data_ptr(), ctx.noise.data_ptr() if ctx.noise is not None else None,
                       gH.data_ptr(), seed, offset, ctx.offset_tensor.data_ptr() if ctx.offset_tensor is not None else None,
                       voice_offset, B, T, NB, hop, _stream())
-        g_out = g if ctx.needs_input_grad[6] else None
         return gH.view(H_shape).to(H_dtype), None, None, None, None, None, g_out, None
 
 

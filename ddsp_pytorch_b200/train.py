@@ -38,7 +38,8 @@ class Zak(nn.Module):
 
 
 def allreduce_mean_(params, bucket_bytes: int = 25 << 20) -> int:
-    """Average .grad over ranks in flat fp32 buckets (one collective per bucket).  Returns the number of collectives."""
+    """Average .grad over ranks in flat fp32 buckets (one collective per bucket) -- the plain, blocking form for gradients
+    that live in their own tensors.  Returns the number of collectives.  The Trainer itself uses `GradBuckets`."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
         return 0
     world = dist.get_world_size()
@@ -61,12 +62,102 @@ def allreduce_mean_(params, bucket_bytes: int = 25 << 20) -> int:
     return n_coll
 
 
+class GradBuckets:
+    """Gradient averaging the way stock DDP does it, without DDP: the trainable parameters are packed, in
+    REVERSE registration order (the order backward produces their gradients), into persistent flat fp32 buckets and every
+    `.grad` is a view into its bucket -- no concatenate / copy-back round trip.  In an eager multi-rank step a
+    post-accumulate hook counts a bucket's gradients in and launches its all-reduce asynchronously the moment the last
+    one has been written, so the collective runs on NCCL's stream under the rest of backward; `finish()` launches whatever
+    was not triggered, waits, and divides by the world size.  The CUDA-graph step keeps the hooks disarmed and reduces the
+    buckets between its two graphs."""
+
+    def __init__(self, params, bucket_bytes: int = 4 << 20):
+        self.params = [p for p in params if p.requires_grad]
+        self.flats, self.members, self.views = [], [], {}
+        cur, size = [], 0
+        for p in reversed(self.params):
+            if cur and size + p.numel() * 4 > bucket_bytes:
+                self._close(cur)
+                cur, size = [], 0
+            cur.append(p)
+            size += p.numel() * 4
+        if cur:
+            self._close(cur)
+        self.bucket_of = {id(p): b for b, ps in enumerate(self.members) for p in ps}
+        self.pending = [0] * len(self.flats)
+        self.launched = [False] * len(self.flats)
+        self.works = []
+        self.armed = False
+        self.n_collectives = 0
+        for p in self.params:
+            p.register_post_accumulate_grad_hook(self._hook)
+
+    def _close(self, ps):
+        dev, n = ps[0].device, sum(p.numel() for p in ps)
+        flat = torch.zeros(n, dtype=torch.float32, device=dev)
+        off = 0
+        for p in ps:
+            self.views[id(p)] = flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+        self.flats.append(flat)
+        self.members.append(ps)
+
+    @staticmethod
+    def _multi() -> bool:
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+    def zero(self, arm: bool = True) -> None:
+        """Start of a step: zero the buckets, make every .grad the bucket view (autograd accumulates into it in place)."""
+        for flat in self.flats:
+            flat.zero_()
+        for p in self.params:
+            v = self.views[id(p)]
+            if p.grad is None or p.grad.data_ptr() != v.data_ptr():
+                p.grad = v
+        self.pending = [len(ps) for ps in self.members]
+        self.launched = [False] * len(self.flats)
+        self.works = []
+        self.armed = bool(arm) and self._multi()
+
+    def _launch(self, b: int) -> None:
+        self.launched[b] = True
+        self.works.append(dist.all_reduce(self.flats[b], op=dist.ReduceOp.SUM, async_op=True))
+        self.n_collectives += 1
+
+    def _hook(self, p) -> None:
+        if not self.armed:
+            return
+        b = self.bucket_of[id(p)]
+        self.pending[b] -= 1
+        if self.pending[b] == 0 and not self.launched[b]:
+            self._launch(b)
+
+    def finish(self) -> int:
+        """After backward: every bucket reduced (those no hook triggered are launched now, in bucket order on all ranks),
+        waited for and divided by the world size.  Returns the number of collectives of this step."""
+        if not self._multi():
+            self.armed = False
+            return 0
+        for b in range(len(self.flats)):
+            if not self.launched[b]:
+                self._launch(b)
+        for w in self.works:
+            w.wait()
+        world = dist.get_world_size()
+        for flat in self.flats:
+            flat.div_(world)
+        n, self.works, self.armed = len(self.works), [], False
+        return n
+
+
 class Trainer:
     def __init__(self, conf, device, amp: bool = False, lr: float = 1e-3, noise_seed: Optional[int] = None,
                  voice_offset: int = 0, synth=None, loss=None, graph: bool = False,
-                 device_counter: Optional[bool] = None):
+                 device_counter: Optional[bool] = None, global_batch: Optional[int] = None, bucket_bytes: int = 4 << 20):
         """graph=True: the whole step (forward, backward, gradient all-reduce, Adam) is captured once as a CUDA graph on
-        the first call and replayed afterwards (fp32 only; batches are copied into static buffers)."""
+        the first call and replayed afterwards (fp32 only; batches are copied into static buffers).
+        global_batch: total voices over all ranks; needed only when the ranks' shards differ in size -- the local loss is
+        then weighted by B_local * world / global_batch so that the averaged gradient is the full-batch gradient."""
         self.device = torch.device(device)
         self.graph = bool(graph) and self.device.type == "cuda" and not amp
         self.zak = Zak(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth, loss=loss,
@@ -80,32 +171,53 @@ class Trainer:
         self.amp = bool(amp) and self.device.type == "cuda"
         self.scaler = torch.amp.GradScaler("cuda", enabled=self.amp)
         self.steps = 0
+        self.global_batch = global_batch
+        self.last_collectives = 0
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
             for p in self.zak.parameters():             # same initial weights everywhere
                 dist.broadcast(p.data, src=0)
+        self.buckets = GradBuckets(self.zak.parameters(), bucket_bytes=bucket_bytes)
+
+    def _loss_weight(self, batch) -> float:
+        if self.global_batch is None or not GradBuckets._multi():
+            return 1.0
+        return float(batch["f0"].shape[0]) * dist.get_world_size() / float(self.global_batch)
 
     def _graphed_step(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
-        multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-        params = list(self.zak.parameters())
+        multi = GradBuckets._multi()
         if self._g is None:
             self._static = {k: v.clone() for k, v in batch.items()}
+            weight = self._loss_weight(batch)
 
             def fwd_bwd():
+                self.buckets.zero(arm=False)                # in-place: the gradients keep their addresses across replays
                 loss = self.zak.training_loss(self._static)
-                loss.backward()
+                (loss * weight if weight != 1.0 else loss).backward()
                 return loss.detach()
 
+            # warm-up outside capture (allocator, cuDNN plans, twiddle tables, Adam state) on the real objects, then put
+            # parameters, optimizer state and the noise counter back: the captured step is the FIRST step of the trajectory,
+            # exactly as in the eager trainer
+            keep_p = [p.detach().clone() for p in self.zak.parameters()]
+            keep_b = [b_.detach().clone() for b_ in self.zak.buffers()]
             side = torch.cuda.Stream(self.device)
             side.wait_stream(torch.cuda.current_stream(self.device))
-            with torch.cuda.stream(side):       # warm-up outside capture (allocator, cuDNN plans, twiddle tables, Adam state)
+            with torch.cuda.stream(side):
                 for _ in range(3):
-                    self.opt.zero_grad(set_to_none=True)
                     fwd_bwd()
-                    allreduce_mean_(params)
+                    self.buckets.finish()
                     self.opt.step()
             torch.cuda.current_stream(self.device).wait_stream(side)
             torch.cuda.synchronize(self.device)
-            self.opt.zero_grad(set_to_none=True)            # gradients are (re)created inside the graph's memory pool
+            with torch.no_grad():
+                for p, k in zip(self.zak.parameters(), keep_p):
+                    p.copy_(k)
+                for b_, k in zip(self.zak.buffers(), keep_b):
+                    b_.copy_(k)
+                for st in self.opt.state.values():          # Adam moments and the device-side step counter back to zero
+                    for v in st.values():
+                        if torch.is_tensor(v):
+                            v.zero_()
             # Two graphs with the NCCL all-reduce between them (eager, on the same stream) when there are several ranks;
             # with one rank the optimizer step is captured into the same graph.
             self._g = torch.cuda.CUDAGraph()
@@ -115,28 +227,31 @@ class Trainer:
                     self.opt.step()
             self._g_opt = None
             if multi:
-                allreduce_mean_(params)
                 self._g_opt = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(self._g_opt, pool=self._g.pool()):
                     self.opt.step()
-            self.steps += 3
         for k, v in batch.items():
             self._static[k].copy_(v)
         self._g.replay()
         if self._g_opt is not None:
-            allreduce_mean_(params)
+            self.buckets.launched = [False] * len(self.buckets.flats)
+            self.buckets.works = []
+            self.last_collectives = self.buckets.finish()
             self._g_opt.replay()
         self.steps += 1
-        return self._loss
+        return self._loss.clone()
 
     def training_step(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
         if self.graph:
             return self._graphed_step(batch)
-        self.opt.zero_grad(set_to_none=True)
+        self.buckets.zero(arm=True)
+        weight = self._loss_weight(batch)
         with torch.autocast("cuda", dtype=torch.float16, enabled=self.amp):
             loss = self.zak.training_loss(batch)
-        self.scaler.scale(loss).backward()
-        allreduce_mean_(list(self.zak.parameters()))    # before unscale_: every rank then sees the same inf/nan verdict
+        # the buckets' all-reduces start from the gradient hooks while backward is still running; they carry the SCALED
+        # gradients, so every rank sees the same inf/nan verdict in unscale_
+        self.scaler.scale(loss * weight if weight != 1.0 else loss).backward()
+        self.last_collectives = self.buckets.finish()
         if self.amp:
             self.scaler.unscale_(self.opt)
         self.scaler.step(self.opt)

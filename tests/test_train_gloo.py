@@ -115,6 +115,51 @@ def test_two_rank_gradient_average_equals_full_batch():
         assert float((got - v).abs().max()) <= 1e-4 * float(v.abs().max()) + 1e-12, k   # fp32 summation order differs
 
 
+def _worker_overlap(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ddsp_pytorch_b200.sharding import voice_shard
+        from ddsp_pytorch_b200.train import Trainer, synthetic_batch
+        conf = small_conf()
+        lo, hi = voice_shard(3, world, rank)                         # 2 + 1 voices: unequal shards
+        torch.manual_seed(0)
+        tr = Trainer(conf, "cpu", synth=(_Osc(conf), _Noise(conf, lo), _Reverb(conf)), loss=_Loss(), global_batch=3,
+                     bucket_bytes=1024)
+        before = {k: p.detach().clone() for k, p in tr.zak.named_parameters()}
+        tr.training_step(synthetic_batch(conf, hi - lo, "cpu", seed=1, voice_offset=lo))
+        if rank == 0:
+            ret["grads"] = {k: p.grad.clone().numpy() for k, p in tr.zak.named_parameters() if p.grad is not None}
+            ret["collectives"] = tr.last_collectives
+            ret["buckets"] = len(tr.buckets.flats)
+            ret["views"] = all(p.grad.data_ptr() == tr.buckets.views[id(p)].data_ptr() for p in tr.buckets.params)
+            ret["moved"] = any(not torch.equal(before[k], p.detach()) for k, p in tr.zak.named_parameters())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_overlapped_bucket_allreduce_with_unequal_shards():
+    """Trainer.training_step on 2 gloo ranks: gradients live in the flat buckets (views), the per-bucket all-reduces are
+    launched from the gradient hooks during backward, and with shards of 2 + 1 voices the weighted average is the
+    full-batch gradient."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ret = mp.Manager().dict()
+    mp.spawn(_worker_overlap, args=(2, port, ret), nprocs=2, join=True)
+    from ddsp_pytorch_b200.train import synthetic_batch
+    conf = small_conf()
+    tr = _make(conf, 0)
+    tr.buckets.zero()
+    tr.zak.training_loss(synthetic_batch(conf, 3, "cpu", seed=1)).backward()
+    want = {k: p.grad.clone() for k, p in tr.zak.named_parameters() if p.grad is not None}
+    assert ret["buckets"] > 2 and ret["collectives"] == ret["buckets"] and ret["views"] and ret["moved"]
+    assert set(want) == set(ret["grads"])
+    for k, v in want.items():
+        got = torch.from_numpy(ret["grads"][k])
+        assert float((got - v).abs().max()) <= 1e-4 * float(v.abs().max()) + 1e-12, k
+
+
 def test_checkpoint_layout_and_resume(tmp_path):
     from ddsp_pytorch_b200.train import synthetic_batch
     conf = small_conf()
