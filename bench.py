@@ -41,11 +41,12 @@ def parse_args():
     p.add_argument("--sample-rate", type=int, default=48000)
     p.add_argument("--seconds", type=float, default=4.0)
     p.add_argument("--hop", type=int, default=512)
-    p.add_argument("--cpu-voices", type=int, default=2, help="voices in the bounded CPU sample")
+    p.add_argument("--cpu-voices", type=int, default=8, help="voices in the bounded CPU sample (SURVEY 8d: an 8-voice chunk)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
-    p.add_argument("--e2e-chunk", type=int, default=64, help="voices per chunk of the host pipeline")
+    p.add_argument("--e2e-chunk", type=int, default=0, help="voices per chunk of the host pipeline (0: about 16 chunks per rank)")
+    p.add_argument("--equal-count-shards", action="store_true", help="shard by voice count instead of by work")
     return p.parse_args()
 
 
@@ -126,11 +127,24 @@ def cpu_step(O, f0, c, a, H, g, sh):
     return y
 
 
+def cpu_sample_voices(args, sh) -> int:
+    """Voices in the bounded CPU sample: --cpu-voices, cut down so the fp32 autograd graph of the oracle (about a dozen
+    live [voices, N, K] tensors) stays below a third of the host memory that is free right now."""
+    want = max(1, min(args.cpu_voices, sh["B"]))
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 64 << 30
+    per_voice = 14 * 4.0 * sh["N"] * sh["K"]
+    return max(1, min(want, int(avail / 3 / per_voice)))
+
+
 def cpu_measure(args, sh, steps: int, warmup: int):
     from oracle import ddsp_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    Bc = max(1, min(args.cpu_voices, sh["B"]))
+    Bc = cpu_sample_voices(args, sh)
     f0, c, a, H = O.synthetic_controls(Bc, sh["T"], sh["K"], sh["NB"], sh["sr"], sh["hop"], seed=1234 + 4)
     g = torch.randn(Bc, sh["N"], generator=torch.Generator().manual_seed(99))
     for _ in range(warmup):
@@ -140,11 +154,12 @@ def cpu_measure(args, sh, steps: int, warmup: int):
         t0 = time.perf_counter()
         cpu_step(O, f0, c, a, H, g, sh)
         times.append(time.perf_counter() - t0)
-    best = min(times)
-    return {"value": Bc * sh["N"] / best, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{Bc} of the {sh['B']} voices (same shapes), oracle/ddsp_oracle.py in fp32 torch eager, "
-                      f"best of {steps} after {warmup} warm-up; median {statistics.median(times):.2f} s/step",
-            "ms_per_step": best * 1e3, "median_ms_per_step": statistics.median(times) * 1e3}
+    mean = sum(times) / len(times)
+    return {"value": Bc * sh["N"] / mean, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{Bc} of the {sh['B']} voices (same shapes), oracle/ddsp_oracle.py in fp32 torch eager incl. the reference's CPU "
+                      f"noise draw, mean of {steps} step(s) after {warmup} warm-up ({mean:.2f} s/step, best {min(times):.2f} s)",
+            "ms_per_step": mean * 1e3, "best_ms_per_step": min(times) * 1e3, "steps_run": steps, "warmup_run": warmup,
+            "voices": Bc}
 
 
 _JSON_FD = None
@@ -171,21 +186,22 @@ def emit(line):
 
 
 def run_reference(args):
+    """The reference's CPU implementation of the path (the oracle port: /root/reference does not travel to the GPU box) on
+    all host threads; every step is one fwd+bwd of an 8-voice chunk of the workload and exactly --steps steps
+    after --warmup warm-up steps are run and reported."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     sh = shapes(args)
     steps, warmup = max(1, args.steps), max(0, args.warmup)
-    # bounded: each step is a cpu-voices sample (~seconds); cap the count so the run ends within minutes
-    steps_run, warm_run = min(steps, 5), min(warmup, 1)
-    res = cpu_measure(args, sh, steps_run, warm_run)
+    res = cpu_measure(args, sh, steps, warmup)
     line = {"impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, sh, {"steps_run": steps_run, "warmup_run": warm_run}),
+            "config": workload_config(args, sh),
             "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "step_definition": f"one step = fwd+bwd of a {res['voices']}-voice chunk; value = chunk samples / mean step time"}
     emit(line)
 
 
@@ -222,7 +238,9 @@ def run_b200(args):
     import torch.distributed as dist
     import ddsp_pytorch_b200 as d
     from ddsp_pytorch_b200 import _lib, ops
-    from ddsp_pytorch_b200.synthetic import synthetic_controls
+    from ddsp_pytorch_b200.host_pipeline import HostSynthPipeline, bind_to_gpu_numa_node, default_chunk
+    from ddsp_pytorch_b200.sharding import balanced_voice_shards, voice_shard, voice_work
+    from ddsp_pytorch_b200.synthetic import synthetic_controls, synthetic_f0
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -231,18 +249,29 @@ def run_b200(args):
         raise RuntimeError("bench.py --impl b200 needs a CUDA device; there is no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(local)                 # before any pinned allocation: host buffers local to the GPU's PCIe root
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     sh = shapes(args)
-    from ddsp_pytorch_b200.sharding import voice_shard
-    v_lo, v_hi = voice_shard(sh["B"], world, rank)      # contiguous voice range of this rank, no data-path collective
-    Bl = v_hi - v_lo
     T, N, K, NB, sr, hop = sh["T"], sh["N"], sh["K"], sh["NB"], sh["sr"], sh["hop"]
     conf = d.Config(sample_rate=sr, hop_length=hop, n_harmonics=K, n_noise_filters=NB)
+    data_seed = 1234 + 4
+
+    # ---- voice shards: contiguous ranges of equal WORK (active harmonics depend on pitch), no data-path collective ----
+    work = voice_work(synthetic_f0(sh["B"], T, sr, hop, seed=data_seed), K, sr, hop)      # every rank: all voices' pitch tracks
+    if args.equal_count_shards:
+        ranges = [voice_shard(sh["B"], world, r) for r in range(world)]
+    else:
+        ranges = balanced_voice_shards(work.tolist(), world)
+    loads = [float(work[lo:hi].sum()) for lo, hi in ranges]
+    v_lo, v_hi = ranges[rank]
+    Bl = v_hi - v_lo
 
     # ---- synthetic inputs, generated on the host, this rank's voices only ------------
-    f0h, ch, ah, Hh = synthetic_controls(Bl, T, K, NB, sr, hop, seed=1234 + 4, voice_offset=v_lo)
-    gh = torch.randn(Bl, N, generator=torch.Generator().manual_seed(99 + rank))
+    f0h, ch, ah, Hh = synthetic_controls(Bl, T, K, NB, sr, hop, seed=data_seed, voice_offset=v_lo)
+    gh = torch.empty(Bl, N)
+    for b in range(Bl):                                 # upstream gradient keyed by global voice: the same for every sharding
+        gh[b] = torch.randn(N, generator=torch.Generator().manual_seed(99_000_000 + v_lo + b))
     host = [t.pin_memory() for t in (f0h, ch, ah, Hh, gh)]
     f0, c, a, H, g = (t.to(dev) for t in host)
     c.requires_grad_(True); a.requires_grad_(True); H.requires_grad_(True)
@@ -259,11 +288,20 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def gather_floats(vals):
+        t = torch.tensor(vals, device=dev, dtype=torch.float64)
+        if world == 1:
+            return [t.tolist()]
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [o.tolist() for o in out]
+
     seed, voff = 7, v_lo
     calls = torch.zeros(1, dtype=torch.int32, device=dev)      # device-side call counter: fresh Philox offset per step
+    lib = _lib.load()
 
     def step_body():
-        """resident inputs -> y = noise(H); y += osc(f0,c,a); backward from g.  6 launches of this repo's kernels."""
+        """resident inputs -> y = noise(H); y += osc(f0,c,a); backward from g."""
         calls.add_(1)
         y = ops.filtered_noise(H, hop, seed=seed, offset=0, voice_offset=voff, offset_tensor=calls)
         y = ops.oscillator_bank(f0, c, a, sr, hop, out=y)
@@ -274,6 +312,9 @@ def run_b200(args):
         c.grad = a.grad = H.grad = None
         return step_body()
 
+    n0 = lib.ddsp_launch_count()
+    eager_step()
+    launches_per_step = int(lib.ddsp_launch_count() - n0)       # kernels of libddsp_b200.so in one step (counted by the library)
     step = eager_step
     if not args.no_graph:
         # the step is launch-bound once the voices are spread over 8 GPUs (1.3 ms of kernels): capture it once and
@@ -302,23 +343,26 @@ def run_b200(args):
         step()
     e1.record()
     barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
+    my_ms = e0.elapsed_time(e1)
+    ms = max_over_ranks(my_ms)
     clocks = sampler.stop(t_load0, time.time()) if sampler else None
     value = sh["B"] * N * args.steps / (ms * 1e-3)
+    rank_ms = [v[0] / args.steps for v in gather_floats([my_ms])]
 
-    # ---- end to end through the module API with host buffers -----------------------------------
+    # ---- end to end through the package's host pipeline: pinned host buffers in, pinned host buffers out ----------
     e2e = None
     if not args.no_e2e:
-        from ddsp_pytorch_b200.host_pipeline import HostSynthPipeline
-        pipe = HostSynthPipeline(conf, dev, chunk_voices=args.e2e_chunk, seed=seed, voice_offset=voff)
-        outs = [torch.empty(s, dtype=torch.float32).pin_memory() for s in ((Bl, T, K), (Bl, T, 1), (Bl, T, NB))]
+        chunk = args.e2e_chunk if args.e2e_chunk > 0 else default_chunk(Bl)
+        pipe = HostSynthPipeline(conf, dev, chunk_voices=chunk, seed=seed, voice_offset=voff)
+        outs = [torch.empty(s_, dtype=torch.float32).pin_memory() for s_ in ((Bl, T, K), (Bl, T, 1), (Bl, T, NB))]
+        y_host = torch.empty(Bl, N, dtype=torch.float32).pin_memory()
         h2d = sum(t.numel() * 4 for t in host)
-        d2h = sum(t.numel() * 4 for t in outs)
+        d2h = sum(t.numel() * 4 for t in outs) + y_host.numel() * 4
 
         def e2e_step():
-            # public API call: pinned host controls + upstream gradient in, pinned host gradients out; returns once
-            # the host owns them (copies and kernels of different voice chunks overlap on three streams)
-            pipe.step(*host, *outs)
+            # public API call: pinned host controls + upstream gradient in; synthesised audio and the three gradients
+            # out to pinned host memory; returns once the host owns them
+            pipe.step(*host, *outs, y_out=y_host)
 
         for _ in range(max(args.warmup, 3)):
             e2e_step()
@@ -328,14 +372,21 @@ def run_b200(args):
             e2e_step()
         e1.record()
         barrier()
-        ems = max_over_ranks(e0.elapsed_time(e1))
-        e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
-               "d2h_bytes_per_step": d2h * world, "ms_per_step": ems / args.steps,
-               "path": f"HostSynthPipeline.step: pinned host f0,c,a,H,g -> {args.e2e_chunk}-voice chunks on copy-in / compute / copy-out streams "
-                       "(ops.filtered_noise + ops.oscillator_bank, backward) -> grads in pinned host memory"}
+        my_ems = e0.elapsed_time(e1)
+        ems = max_over_ranks(my_ems)
+        per_rank = gather_floats([my_ems / args.steps, float(h2d), float(d2h), float(Bl), -1.0 if numa is None else float(numa)])
+        e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(sum(r[1] for r in per_rank)), "d2h_bytes_per_step": int(sum(r[2] for r in per_rank)),
+               "ms_per_step": ems / args.steps, "chunk_voices": chunk, "chunks_per_rank": -(-Bl // chunk),
+               "launches_per_step_rank0": pipe.launches_per_step,
+               "per_rank": [{"voices": int(r[3]), "ms_per_step": r[0], "h2d_GBps": r[1] / (r[0] * 1e-3) / 1e9,
+                             "d2h_GBps": r[2] / (r[0] * 1e-3) / 1e9, "numa_node": None if r[4] < 0 else int(r[4])} for r in per_rank],
+               "result": "synthesised audio y and the gradients of c, a, H (the forward's and the backward's outputs) in pinned host memory",
+               "path": "HostSynthPipeline.step: pinned host f0,c,a,H,g -> voice chunks on copy-in / compute / copy-out streams "
+                       "(ddsp_noise_forward + ddsp_osc_forward(accumulate) + ddsp_osc_backward + ddsp_noise_backward per chunk) "
+                       "-> y, gc, ga, gH in pinned host memory"}
 
-    # ---- per-kernel device times (rank 0's shard) and the roofline of the dominant kernel -------
-    lib = _lib.load()
+    # ---- per-kernel device times (this rank's shard) and the roofline of the dominant kernel -------
     st = torch.cuda.current_stream().cuda_stream
     state = torch.empty(lib.ddsp_osc_state_bytes(Bl, T, K), dtype=torch.uint8, device=dev)
     scratch = torch.empty(lib.ddsp_osc_backward_scratch_bytes(Bl, T, K), dtype=torch.uint8, device=dev)
@@ -343,7 +394,7 @@ def run_b200(args):
     gc = torch.empty(Bl, T, K, device=dev); ga = torch.empty(Bl, T, device=dev); gH = torch.empty(Bl, T, NB, device=dev)
     P = lambda t: t.data_ptr()  # noqa: E731
     cd_, ad_, Hd_ = c.detach(), a.detach(), H.detach()
-    calls = {
+    kcalls = {
         "osc_prepare_kernel": lambda: _lib.call("ddsp_osc_prepare", P(f0), P(cd_), P(state), Bl, T, K, hop, sr, st),
         "osc_synth_kernel": lambda: _lib.call("ddsp_osc_synthesize", P(f0), P(ad_), P(state), P(y), P(z), 0, Bl, T, K, hop, sr, st),
         "osc_grad_kernel": lambda: _lib.call("ddsp_osc_grad_segments", P(g), P(f0), P(ad_), P(z), P(state), P(scratch), Bl, T, K, hop, sr, st),
@@ -351,48 +402,51 @@ def run_b200(args):
         "noise_fwd_kernel": lambda: _lib.call("ddsp_noise_forward", P(Hd_), None, P(y), 0, seed, 0, None, voff, Bl, T, NB, hop, st),
         "noise_bwd_kernel": lambda: _lib.call("ddsp_noise_backward", P(g), None, P(gH), seed, 0, None, voff, Bl, T, NB, hop, st),
     }
-    kernels_ms = {name: time_call(fn) for name, fn in calls.items()}
+    kernels_ms = {name: time_call(fn) for name, fn in kcalls.items()}
     fp32_peak = ops.probe_fp32_fma_tflops()
+    props = torch.cuda.get_device_properties(dev)
+    sm_max_mhz = (clocks or {}).get("sm_max_mhz") or 1965.0
+    fp32_nominal = props.multi_processor_count * 128 * 2 * sm_max_mhz * 1e6 / 1e12       # 128 FMA lanes per SM per clock
     active = active_harmonic_samples(f0.view(Bl, T), K, sr, hop)
     dom = max(kernels_ms, key=kernels_ms.get)
-    # SURVEY §8d algorithmic work per harmonic-sample: 6 flops forward, 12 flops backward
-    flops_per_hs = {"osc_synth_kernel": 6.0, "osc_grad_kernel": 12.0}.get(dom)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except OSError:
         pass
+    # DRAM bytes of one launch of the dominant kernel from the ncu --set full capture of THIS shard size (profiles/traffic_r02.json
+    # is keyed by kernel and voices per launch); absent for shard sizes that were not captured
     traffic = None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
-    except (OSError, ValueError):
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic_r02.json"))).get(dom, {}).get(str(Bl))
+    except (OSError, ValueError, AttributeError):
         pass
     roofline = None
-    if flops_per_hs:
-        ach = flops_per_hs * active / (kernels_ms[dom] * 1e-3) / 1e12
-        roofline = {"kernel": dom, "bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach / fp32_peak,
-                    "traffic": traffic, "launch_ms": kernels_ms[dom],
+    # SURVEY §8d counts 6 flop (forward) / 12 flop (backward) per harmonic-sample; both kernels EXECUTE 4 FMA-pipe lane operations
+    # per harmonic-sample (recurrence FFMA2 + FADD2, two dot-product FFMA2), i.e. 8 flop of pipe capacity.  `frac` is the executed
+    # figure (the one ncu's sm__pipe_fma_cycles_active must agree with); the SURVEY-count figure is printed beside it.
+    survey_flop = {"osc_synth_kernel": 6.0, "osc_grad_kernel": 12.0}.get(dom)
+    if survey_flop:
+        sec = kernels_ms[dom] * 1e-3
+        executed = 8.0 * active / sec / 1e12
+        algo_bytes = 4.0 * (Bl * N * 2 + Bl * T * (K + 2))
+        roofline = {"kernel": dom, "bound": "fp32", "achieved": executed, "peak": fp32_peak, "unit": "TFLOP/s",
+                    "frac": executed / fp32_peak, "traffic": traffic, "launch_ms": kernels_ms[dom],
                     "peak_source": "FFMA-chain probe (ddsp_probe_fp32_fma) measured in this run; MEASURED_PEAKS.json has no FP32 figure",
-                    "work": f"{flops_per_hs:g} flop x {active:.4g} active harmonic-samples on this rank "
-                            f"(nominal K would be {Bl * N * K:.4g}; Nyquist-masked harmonics are skipped)",
-                    "achieved_if_nominal_K": flops_per_hs * Bl * N * K / (kernels_ms[dom] * 1e-3) / 1e12,
-                    # what the kernel itself executes: 4 FMA-pipe lane operations per harmonic-sample in either direction (3 FMA +
-                    # 1 add, issued as packed FFMA2/FADD2 pairs; counted as 8 flop of pipe capacity) -- fewer than SURVEY's
-                    # count for the backward, so `frac` above overstates the pipe's occupancy; this is the figure to compare
-                    # with ncu's sm__pipe_fma_cycles_active
-                    "executed": {"pipe_flop_per_harmonic_sample": 8.0,
-                                 "tflops": 8.0 * active / (kernels_ms[dom] * 1e-3) / 1e12,
-                                 "frac_of_peak": 8.0 * active / (kernels_ms[dom] * 1e-3) / 1e12 / fp32_peak},
-                    "hbm": {"algorithmic_bytes": 4.0 * (Bl * N * 2 + Bl * T * (K + 2)),
-                            "achieved_GBps": 4.0 * (Bl * N * 2 + Bl * T * (K + 2)) / (kernels_ms[dom] * 1e-3) / 1e9,
-                            "peak_GBps": peaks.get("hbm_gbs")}}
+                    "peak_nominal": fp32_nominal, "frac_of_nominal": executed / fp32_nominal,
+                    "work": f"8 flop of FMA-pipe capacity (4 lane operations) x {active:.4g} active harmonic-samples on this rank "
+                            f"(nominal K would be {Bl * N * K:.4g}; Nyquist-masked harmonics are skipped, as they contribute 0 in the reference)",
+                    "frac_survey_count": survey_flop * active / sec / 1e12 / fp32_peak,
+                    "survey_count": {"flop_per_harmonic_sample": survey_flop, "tflops": survey_flop * active / sec / 1e12},
+                    "hbm": {"algorithmic_bytes": algo_bytes, "achieved_GBps": algo_bytes / sec / 1e9, "peak_GBps": peaks.get("hbm_gbs")}}
 
-    # fused oscillator + noise, forward + backward (the north star's >= 50 % target): SURVEY §8d flop count / step time
+    # fused oscillator + noise, forward + backward (the north star's >= 50 % target): SURVEY §8d flop count / this rank's step time
     M = 2 * (NB - 1)
     fused_flop = 18.0 * active + 2.0 * (M + M * NB / hop) * Bl * N
-    fused = {"achieved": fused_flop / (ms / args.steps * 1e-3) / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
-             "frac": fused_flop / (ms / args.steps * 1e-3) / 1e12 / fp32_peak,
-             "work": "18 flop x active harmonic-samples + 2(M + M*NB/hop) flop x samples on rank 0, over the whole step"}
+    my_step_s = my_ms / args.steps * 1e-3
+    fused = {"achieved": fused_flop / my_step_s / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
+             "frac": fused_flop / my_step_s / 1e12 / fp32_peak, "frac_of_nominal": fused_flop / my_step_s / 1e12 / fp32_nominal,
+             "work": "SURVEY 8d count: 18 flop x active harmonic-samples + 2(M + M*NB/hop) flop x samples on rank 0, over rank 0's step"}
     if world > 1:
         dist.barrier(device_ids=[local])
     if rank != 0:
@@ -407,12 +461,19 @@ def run_b200(args):
         rt = {k: r[k] for k in ("workload", "deadline_ms", "host_p50_ms", "host_p99_ms", "device_p50_ms", "device_p99_ms")}
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        r = cpu_measure(args, sh, steps=2, warmup=1)
+        r = cpu_measure(args, sh, steps=3, warmup=1)
         cpu = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    mean_load = sum(loads) / len(loads)
+    sharding = {"policy": "equal voice counts" if args.equal_count_shards else "contiguous ranges of equal work (sharding.balanced_voice_shards)",
+                "voices_per_rank": [hi - lo for lo, hi in ranges], "work_max_over_mean": max(loads) / mean_load,
+                "work_per_rank_over_mean": [x / mean_load for x in loads], "ms_per_step_per_rank": rank_ms}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": workload_config(args, sh), "clocks": clocks, "e2e": e2e, "gpu_launches": 6 * args.steps,
-            "roofline": roofline, "roofline_fused": fused, "cpu_baseline": cpu, "kernels_ms": kernels_ms, "fp32_fma_peak_tflops_measured": fp32_peak, "rt_block_latency": rt}
+            "data": "synthetic", "config": workload_config(args, sh), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
+            "roofline": roofline, "roofline_fused": fused, "cpu_baseline": cpu, "kernels_ms": kernels_ms,
+            "fp32_fma_peak_tflops_measured": fp32_peak, "fp32_fma_peak_tflops_nominal": fp32_nominal, "sharding": sharding,
+            "rt_block_latency": rt}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -15,6 +15,7 @@ _p, _i, _u32, _u64, _sz = C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_size_
 SIGNATURES = {
     "ddsp_abi_version": (_i, []),
     "ddsp_last_error": (C.c_char_p, []),
+    "ddsp_launch_count": (C.c_ulonglong, []),
     "ddsp_osc_state_bytes": (_sz, [_i, _i, _i]),
     "ddsp_osc_forward": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "ddsp_osc_prepare": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
@@ -37,8 +38,9 @@ SIGNATURES = {
     "ddsp_conv_backward": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "ddsp_reverb_live": (_i, [_p, _p, _p, _p, _p, _i, _i, _p]),
     "ddsp_mss_count": (C.c_int64, [_i, _i, _i, _i]),
-    "ddsp_mss_forward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, C.c_float, C.c_float, _i, _i, _p]),
-    "ddsp_mss_backward": (_i, [_p, _p, _p, _i, _i, _p]),
+    "ddsp_mss_scratch_bytes": (_sz, [_p, _p, _i, _i, _i]),
+    "ddsp_mss_forward": (_i, [_p, _p, _p, _p, _p, _i, _p, _p, _p, _i, C.c_float, C.c_float, _i, _i, _p]),
+    "ddsp_mss_backward": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _p]),
     "ddsp_rowconv_forward": (_i, [_p, _p, _p, C.c_longlong, _i, _p]),
     "ddsp_rowconv_backward": (_i, [_p, _p, _p, _p, _p, C.c_longlong, _i, _p]),
     "ddsp_ctrl_heads_ldz": (_i, [_i, _i]),

@@ -39,9 +39,9 @@ class MLP(nn.Module):
 
 class Controller(nn.Module):
     """decoder.py:41-116.  The tail -- three Linear heads + modified_sigmoid -- runs as one fused kernel
-    (`ops.controller_heads`) whenever its input is a CUDA tensor; the parameters stay the three
-    nn.Linear modules of the reference, so state dicts are unchanged.  On CPU tensors (the gloo tests) the plain torch
-    expression is used -- that is host-side test plumbing, not a product path."""
+    (`ops.controller_heads`); the parameters stay the three nn.Linear modules of the reference, so state
+    dicts are unchanged.  There is no CPU fallback: CPU tensors raise.  `fused_tail=False` is an explicit opt-out that
+    evaluates the tail as the reference writes it (three nn.Linear + modified_sigmoid in torch), for comparisons."""
 
     def __init__(self, conf, fused_tail: bool = True):
         super().__init__()
@@ -64,7 +64,7 @@ class Controller(nn.Module):
         x = torch.cat((lf0, lld), dim=-1)
         x, h = self.gru(x) if hidden is None else self.gru(x, hidden)
         x = self.mlp_gru(torch.cat((x, lf0, lld), dim=-1))
-        if self.fused_tail and x.is_cuda:
+        if self.fused_tail:
             c, a, H = ops.controller_heads(x, self.dense_harmonic.weight, self.dense_harmonic.bias, self.dense_loudness.weight,
                                            self.dense_loudness.bias, self.dense_filter.weight, self.dense_filter.bias)
         else:
@@ -78,19 +78,18 @@ class Controller(nn.Module):
 class Decoder(nn.Module):
     """decoder.py:119-147 with the synthesis modules of this package."""
 
-    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None, device_counter: bool = False):
-        """`synth`: optional (harmonics, noise, reverb) module triple replacing this package's CUDA modules --
-        used by the CPU-only multi-process tests to drive the trainer with the oracle; never by the product path."""
+    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, device_counter: bool = False, fused_tail: bool = True):
         super().__init__()
-        self.controller = Controller(conf)
-        if synth is None:
-            synth = (OscillatorBank(conf), FilteredNoise(conf, seed=noise_seed, voice_offset=voice_offset,
-                                                         device_counter=device_counter), Reverb(conf))
-        self.harmonics, self.noise, self.reverb = synth
+        self.controller = Controller(conf, fused_tail=fused_tail)
+        self.harmonics = OscillatorBank(conf)
+        self.noise = FilteredNoise(conf, seed=noise_seed, voice_offset=voice_offset, device_counter=device_counter)
+        self.reverb = Reverb(conf)
 
     def forward(self, z):
         ctrl = self.controller(z)
-        return self.reverb(self.harmonics(ctrl) + self.noise(ctrl))
+        # `harmonics + noise` (decoder.py:132) without the separate add: the oscillator kernel accumulates into the noise
+        dry = self.harmonics(ctrl, out=self.noise(ctrl))
+        return self.reverb(dry)
 
     def forward_live(self, z, hidden):
         ctrl, hidden = self.controller(z, hidden)

@@ -1,9 +1,13 @@
 // Library-wide pieces of the C ABI: version, per-thread error text, FP32 peak probe.
 #include <stdarg.h>
+#include <atomic>
 #include "ddsp_common.cuh"
 
 namespace ddsp {
 static thread_local char g_err[512] = "";
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -33,6 +37,8 @@ using namespace ddsp;
 extern "C" int ddsp_abi_version(void) { return DDSP_B200_ABI_VERSION; }
 
 extern "C" const char* ddsp_last_error(void) { return g_err; }
+
+extern "C" unsigned long long ddsp_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int ddsp_probe_fp32_fma(float* out, int blocks, int threads, int iters, void* stream) {
     DDSP_REQUIRE(out && blocks > 0 && threads > 0 && threads <= 1024 && iters > 0, "ddsp_probe_fp32_fma: bad arguments");

@@ -8,6 +8,7 @@
 namespace ddsp {
 
 void set_error(const char* fmt, ...);
+void count_launch();    // every kernel this library launches (or records into a capturing stream) passes through here
 
 #define DDSP_REQUIRE(cond, ...)                 \
     do {                                        \
@@ -20,6 +21,7 @@ void set_error(const char* fmt, ...);
 #define DDSP_CHECK_LAUNCH(name)                                                          \
     do {                                                                                 \
         cudaError_t e__ = cudaGetLastError(); /* clears it: a failed launch must not poison later calls */ \
+        ::ddsp::count_launch();                                                          \
         if (e__ != cudaSuccess) {                                                        \
             ::ddsp::set_error("%s: launch failed: %s", name, cudaGetErrorString(e__));   \
             return 2;                                                                    \

@@ -20,11 +20,13 @@ class OscillatorBank(nn.Module):
         self.harmonics = nn.Parameter(torch.arange(1, self.n_harmonics + 1), requires_grad=False)
         self.last_phases = nn.Parameter(torch.zeros(self.n_harmonics, dtype=torch.int64), requires_grad=False)
 
-    def forward(self, x):
+    def forward(self, x, out=None):
+        """`out` (an extension over harmonic_oscillator.py:57-62): a [B,T*hop] fp32 CUDA buffer the result is ADDED into and
+        returned as -- the Decoder passes the filtered noise here, which removes the separate `harmonics + noise` pass."""
         c = x["c"]
         if c.shape[-1] != self.n_harmonics:
             raise RuntimeError(f"OscillatorBank: x['c'] has {c.shape[-1]} harmonics, module has {self.n_harmonics}")
-        return ops.oscillator_bank(x["f0"], c, x["a"], self.sample_rate, self.hop_size)
+        return ops.oscillator_bank(x["f0"], c, x["a"], self.sample_rate, self.hop_size, out=out)
 
     # ---- the reference's public helper methods (harmonic_oscillator.py:24-55; no caller outside the class) -------------
     # forward() above does NOT go through them -- the kernels never build a [B,N,K] tensor.  They are kept for code that
@@ -69,7 +71,8 @@ class FilteredNoise(nn.Module):
         self.voice_offset = int(voice_offset)
         self.calls = 0
         # device_counter: keep the call counter on the device and advance it there, so that a CUDA graph that captured
-        # this forward (and its backward) draws fresh noise on every replay.  Valid for forward -> backward alternation.
+        # this forward (and its backward) draws fresh noise on every replay.  Each forward keeps a snapshot of the counter
+        # for its own backward, so several forwards may precede a backward.
         self.device_counter = bool(device_counter)
         if self.device_counter:
             self.register_buffer("_calls_dev", torch.zeros(1, dtype=torch.int32), persistent=False)

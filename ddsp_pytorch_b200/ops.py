@@ -332,7 +332,6 @@ class _MSSLoss(torch.autograd.Function):
         need_grad = x_pred.requires_grad
         terms = torch.empty(1 + 2 * ns, dtype=torch.float64, device=dev)
         loss = torch.empty((), dtype=torch.float32, device=dev)
-        gx = torch.empty(B, N, dtype=torch.float32, device=dev) if need_grad else None
         nf = (C.c_int * ns)(*[int(v) for v in n_ffts])
         hp = (C.c_int * ns)(*[int(v) for v in hops])
         wins = None
@@ -343,23 +342,32 @@ class _MSSLoss(torch.autograd.Function):
                     raise RuntimeError(f"mss_loss: window of {w.numel()} samples given for n_fft={n}")
             wins = (C.c_void_p * ns)(*[None if w is None else w.data_ptr() for w in keep])
         with torch.cuda.device(dev):
-            _lib.call("ddsp_mss_forward", xp.data_ptr(), xt.data_ptr(), terms.data_ptr(), loss.data_ptr(),
-                      gx.data_ptr() if need_grad else None, C.cast(nf, C.c_void_p), C.cast(hp, C.c_void_p),
+            nbytes = _lib.load().ddsp_mss_scratch_bytes(C.cast(nf, C.c_void_p), C.cast(hp, C.c_void_p), ns, B, N)
+            if nbytes == 0:
+                raise RuntimeError(f"mss_loss: unsupported arguments (n_ffts {list(n_ffts)} must be powers of two in [4,4096] with "
+                                   f"n_fft/2 < N={N}; at most 16 scales)")
+            scratch = _bytes(nbytes, dev)
+            _lib.call("ddsp_mss_forward", xp.data_ptr(), xt.data_ptr(), terms.data_ptr(), loss.data_ptr(), scratch.data_ptr(),
+                      int(need_grad), C.cast(nf, C.c_void_p), C.cast(hp, C.c_void_p),
                       C.cast(wins, C.c_void_p) if wins is not None else None, ns, float(alpha), float(eps), B, N, _stream())
         if need_grad:
-            ctx.save_for_backward(gx)
-        ctx.meta = (x_pred.dtype, B, N)
+            ctx.save_for_backward(scratch)
+        ctx.meta = (x_pred.dtype, B, N, tuple(int(v) for v in n_ffts), tuple(int(v) for v in hops))
         ctx.terms = terms
         return loss
 
     @staticmethod
     def backward(ctx, gloss):
-        (gx,) = ctx.saved_tensors
-        dt, B, N = ctx.meta
+        import ctypes as C
+        (scratch,) = ctx.saved_tensors
+        dt, B, N, n_ffts, hops = ctx.meta
+        ns = len(n_ffts)
         gl = _f32(gloss).view(1)
-        out = torch.empty_like(gx)
-        with torch.cuda.device(gx.device):
-            _lib.call("ddsp_mss_backward", gl.data_ptr(), gx.data_ptr(), out.data_ptr(), B, N, _stream())
+        out = torch.empty(B, N, dtype=torch.float32, device=scratch.device)
+        nf, hp = (C.c_int * ns)(*n_ffts), (C.c_int * ns)(*hops)
+        with torch.cuda.device(scratch.device):
+            _lib.call("ddsp_mss_backward", gl.data_ptr(), scratch.data_ptr(), out.data_ptr(), C.cast(nf, C.c_void_p),
+                      C.cast(hp, C.c_void_p), ns, B, N, _stream())
         return out.to(dt), None, None, None, None, None, None
 
 

@@ -29,3 +29,16 @@ def synthetic_controls(B: int, T: int, K: int, NB: int, sample_rate: int, hop: i
         a[b] = _msig(torch.randn(T, 1, generator=g, dtype=torch.float64))
         H[b] = _msig(torch.randn(T, NB, generator=g, dtype=torch.float64))
     return f0.to(dtype), c.to(dtype), a.to(dtype), H.to(dtype)
+
+
+def synthetic_f0(B: int, T: int, sample_rate: int, hop: int, seed: int, voice_offset: int = 0, dtype=torch.float32):
+    """Only the f0 tracks of `synthetic_controls` (same draws: the pitch is the first thing each voice's generator
+    produces) -> [B,T,1].  Cheap enough for every rank to evaluate for ALL voices when it balances the shards."""
+    f0 = torch.empty(B, T, 1, dtype=torch.float64)
+    t = torch.arange(T, dtype=torch.float64) * hop / sample_rate
+    for b in range(B):
+        g = torch.Generator().manual_seed(seed * 1_000_003 + voice_offset + b)
+        base = 80.0 * (1000.0 / 80.0) ** torch.rand(1, generator=g, dtype=torch.float64)
+        f = base * (1.0 + 0.01 * torch.sin(2.0 * math.pi * 5.0 * t)) + torch.randn(T, generator=g, dtype=torch.float64)
+        f0[b, :, 0] = f.clamp(20.0, sample_rate / 2 - 1.0)
+    return f0.to(dtype)

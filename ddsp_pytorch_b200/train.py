@@ -25,10 +25,10 @@ N_FFTS = [2048, 1024, 512, 256, 128, 64]            # train/train.py:19
 class Zak(nn.Module):
     """Same attribute names as the reference's LightningModule: `model` (Decoder) and `loss` (MSSLoss)."""
 
-    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, synth=None, loss=None, device_counter: bool = False):
+    def __init__(self, conf, noise_seed=None, voice_offset: int = 0, device_counter: bool = False):
         super().__init__()
-        self.model = Decoder(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth, device_counter=device_counter)
-        self.loss = loss if loss is not None else MSSLoss(N_FFTS)
+        self.model = Decoder(conf, noise_seed=noise_seed, voice_offset=voice_offset, device_counter=device_counter)
+        self.loss = MSSLoss(N_FFTS)
 
     def forward(self, batch):
         return self.model(batch)
@@ -152,16 +152,19 @@ class GradBuckets:
 
 class Trainer:
     def __init__(self, conf, device, amp: bool = False, lr: float = 1e-3, noise_seed: Optional[int] = None,
-                 voice_offset: int = 0, synth=None, loss=None, graph: bool = False,
-                 device_counter: Optional[bool] = None, global_batch: Optional[int] = None, bucket_bytes: int = 4 << 20):
+                 voice_offset: int = 0, graph: bool = False, device_counter: Optional[bool] = None,
+                 global_batch: Optional[int] = None, bucket_bytes: int = 4 << 20, zak: Optional[nn.Module] = None):
         """graph=True: the whole step (forward, backward, gradient all-reduce, Adam) is captured once as a CUDA graph on
         the first call and replayed afterwards (fp32 only; batches are copied into static buffers).
         global_batch: total voices over all ranks; needed only when the ranks' shards differ in size -- the local loss is
-        then weighted by B_local * world / global_batch so that the averaged gradient is the full-batch gradient."""
+        then weighted by B_local * world / global_batch so that the averaged gradient is the full-batch gradient.
+        zak: the module to train (anything with `training_loss(batch)`); default: `Zak(conf, ...)`, the reference's model."""
         self.device = torch.device(device)
         self.graph = bool(graph) and self.device.type == "cuda" and not amp
-        self.zak = Zak(conf, noise_seed=noise_seed, voice_offset=voice_offset, synth=synth, loss=loss,
-                       device_counter=self.graph if device_counter is None else device_counter).to(self.device)
+        if zak is None:
+            zak = Zak(conf, noise_seed=noise_seed, voice_offset=voice_offset,
+                      device_counter=self.graph if device_counter is None else device_counter)
+        self.zak = zak.to(self.device)
         if self.graph:      # capturable Adam keeps step counts and the learning rate on the device
             self.opt = torch.optim.Adam(self.zak.parameters(), lr=torch.tensor(lr, device=self.device), capturable=True)
         else:

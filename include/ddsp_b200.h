@@ -32,6 +32,9 @@ extern "C" {
 
 int         ddsp_abi_version(void);
 const char* ddsp_last_error(void);
+/* Number of kernels this library has launched (or recorded into a capturing stream) in this process: the bench's
+ * `gpu_launches` claim is counted from it, not assumed.  No reference counterpart. */
+unsigned long long ddsp_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------
  * Harmonic oscillator bank  --  OscillatorBank.forward, harmonic_oscillator.py:57-62
@@ -163,24 +166,34 @@ int ddsp_reverb_live(float* buffer, const float* x, const float* ir, float* y, v
 /* Elements of one scale's spectrogram: B * (n_fft/2+1) * (1 + N/hop)  (the `mean` denominators of :29-30). */
 int64_t ddsp_mss_count(int B, int N, int n_fft, int hop);
 
+/* Bytes of the caller-owned scratch ddsp_mss_forward fills and ddsp_mss_backward reads: per scale the windowed
+ * gradient frames already overlap-added by their owners (B*N floats plus margins), the spills that crossed a work-item
+ * boundary, and the per-CTA partial loss sums.  Depends on the arguments and the current device only. */
+size_t ddsp_mss_scratch_bytes(const int* n_ffts_host, const int* hops_host, int n_scales, int B, int N);
+
 /* MSSLoss.forward, mss_loss.py:57-68.  x_pred, x_true [B,N].
- *   loss_terms (device, double[1 + 2*n_scales], zeroed here): [0] the loss
+ *   loss_terms (device, double[1 + 2*n_scales]): [0] the loss
  *     sum_s ( sum|Sp-St| + alpha*sum|log2(St+eps)-log2(Sp+eps)| ) / count_s, then per scale the two raw sums;
  *   loss_f32 (device float[1]) or NULL: the loss rounded to fp32;
- *   gx [B,N] or NULL (zeroed here): d loss / d x_pred, produced in the same pass.
- *   n_ffts_host / hops_host: HOST int arrays; n_fft a power of two in [4,4096], n_fft/2 < N;
+ *   scratch: ddsp_mss_scratch_bytes(...) bytes; need_grad != 0 also leaves d loss / d x_pred in it (per scale, owner-
+ *     computes overlap-add -- no floating-point atomics: loss and gradient are bit-reproducible and a voice's gradient
+ *     does not depend on which batch it is evaluated in, up to the exact ratio of the two means);
+ *   n_ffts_host / hops_host: HOST int arrays; n_fft a power of two in [4,4096] (the reference accepts any n_fft:
+ *     INTEGRATION.md, behavioural differences), n_fft/2 < N, at most 16 scales; hop = n_fft/4 (the reference's
+ *     default overlap 0.75) runs the register-tiled kernels, any other hop a generic shared-memory kernel;
  *   windows_host: NULL, or a HOST array of n_scales device pointers (entries may be NULL) to the fp32 analysis
  *     windows [n_fft] -- the reference's `stft.window` buffers (mss_loss.py:23); NULL = periodic Hann rounded
  *     from fp64, which differs from torch.hann_window's fp32 table by an ulp in places: pass the table when the
  *     gradient has to match the reference bin for bin on near-silent input. */
 int ddsp_mss_forward(const float* x_pred, const float* x_true, double* loss_terms, float* loss_f32,
-                     float* gx, const int* n_ffts_host, const int* hops_host,
+                     void* scratch, int need_grad, const int* n_ffts_host, const int* hops_host,
                      const float* const* windows_host, int n_scales, float alpha, float eps, int B, int N,
                      void* stream);
 
-/* Backward of the scalar loss: gx_out = gloss[0] * gx_saved   (gloss: device float scalar). */
-int ddsp_mss_backward(const float* gloss, const float* gx_saved, float* gx_out, int B, int N,
-                      void* stream);
+/* Backward of the scalar loss: gx_out [B,N] = gloss[0] * d loss / d x_pred, gathered from the forward's scratch
+ * (scales in order, then the reflect-padded margins folded back; gloss: device float scalar). */
+int ddsp_mss_backward(const float* gloss, const void* scratch, float* gx_out, const int* n_ffts_host,
+                      const int* hops_host, int n_scales, int B, int N, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Loudness feature  --  LoudnessEncoder.forward, model/autoencoder/encoder.py:141-156

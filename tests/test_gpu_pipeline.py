@@ -1,4 +1,5 @@
-"""HostSynthPipeline (chunked, three streams) must give exactly the gradients of one un-chunked call."""
+"""HostSynthPipeline (chunked, three streams, C-ABI calls into its own slots) must give exactly the audio and the gradients
+of one un-chunked call through the autograd ops."""
 import pytest
 import torch
 
@@ -16,16 +17,23 @@ def test_pipeline_matches_single_call():
     g = torch.randn(B, T * hop, generator=torch.Generator().manual_seed(1))
     host = [t.contiguous().pin_memory() for t in (f0, c, a, H, g)]
     outs = [torch.empty_like(t).pin_memory() for t in (c, a, H)]
+    y_host = torch.empty(B, T * hop).pin_memory()
     pipe = HostSynthPipeline(conf, "cuda:0", chunk_voices=4, slots=2, seed=5, voice_offset=7)
-    pipe.step(*host, *outs)
+    pipe.step(*host, *outs, y_out=y_host)
+    assert pipe.launches_per_step == 6 * 3                 # 3 chunks x (noise fwd, prepare, synth, grad, finalize, noise bwd)
 
     dev = torch.device("cuda:0")
     cd, ad, Hd = (t.to(dev).requires_grad_(True) for t in (c, a, H))
     y = ops.filtered_noise(Hd, hop, seed=5, offset=0, voice_offset=7)
     y = ops.oscillator_bank(f0.to(dev), cd, ad, sr, hop, out=y)
     y.backward(g.to(dev))
+    assert torch.equal(y_host, y.detach().cpu())
     for got, want in zip(outs, (cd.grad, ad.grad, Hd.grad)):
         assert torch.equal(got, want.cpu())
+    # default chunking (about 16 chunks per step, 4..64 voices each) gives the same bits
+    outs2 = [torch.empty_like(t).pin_memory() for t in (c, a, H)]
+    HostSynthPipeline(conf, "cuda:0", seed=5, voice_offset=7).step(*host, *outs2)
+    assert all(torch.equal(p, q) for p, q in zip(outs, outs2))
     # a second step draws fresh noise (call counter) and still matches
     pipe.step(*host, *outs)
     Hd.grad = None

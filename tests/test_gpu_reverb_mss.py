@@ -221,11 +221,31 @@ def test_whole_path_golden(golden):
     assert abs(float(rv.wet.grad) - float(g["g_rev_wet"])) <= 2e-4 * abs(float(g["g_rev_wet"]))
 
 
+def _tied_bin_gradients(xp64, xt64, ffts, thresh=1e-5, alpha=1.0, eps=1e-7):
+    """For every (scale, bin, frame) whose predicted and true power agree to `thresh` relative: the fp64 gradient of that
+    one bin's two L1 terms (mss_loss.py:29-30) w.r.t. x_pred -- flipping the bin's sign changes the total gradient by
+    -2 times this."""
+    from oracle import ddsp_oracle as O
+    out = []
+    for n in ffts:
+        x = xp64.detach().clone().requires_grad_(True)
+        sp, st = O.power_spectrogram(x, n, n // 4), O.power_spectrogram(xt64, n, n // 4)
+        tie = ((sp.detach() - st).abs() / st) < thresh
+        for idx in tie.nonzero().tolist():
+            b, k, f = idx
+            term = ((sp[b, k, f] - st[b, k, f]).abs() + alpha * ((st[b, k, f] + eps).log2() - (sp[b, k, f] + eps).log2()).abs()) / sp.numel()
+            (g,) = torch.autograd.grad(term, x, retain_graph=True)
+            out.append(g)
+    return out
+
+
 def test_mss_gradient_exceedances_are_sign_ties():
     """The two L1 terms put a sign() into d loss / d S_pred.  A bin whose predicted and true power agree to ~1e-6 relative makes
     that sign -- and one windowed sinusoid of the gradient -- arbitrary in fp32, for this kernel and for the reference's own fp32
-    run alike (about one random input in 600 at this shape; found by scratch/fuzz.py, settled by scratch/mss_ties.py).  Every
-    case over the 1e-4 bound must be explained by such a tie; anything else is a defect."""
+    run alike (about one random input in 600 at this shape; found by profiles/probes/fuzz.py, settled by profiles/probes/mss_ties.py).
+    Strict form: for every case over the 1e-4 bound, the fp64 oracle gradient with the sign of (a subset of) its tied bins
+    flipped must match the kernel within the same 1e-4 -- a tie explains exactly that much and nothing else."""
+    import itertools
     from ddsp_pytorch_b200 import ops
     from oracle import ddsp_oracle as O
     gen = torch.Generator().manual_seed(12345)
@@ -236,10 +256,61 @@ def test_mss_gradient_exceedances_are_sign_ties():
         O.mss_loss(xpd, xt.double(), ffts).backward()
         xc = xp.cuda().requires_grad_(True)
         ops.mss_loss(xc, xt.cuda(), ffts).backward()
-        err = float((xc.grad.double().cpu() - xpd.grad).abs().max() / xpd.grad.abs().max())
+        got, want = xc.grad.double().cpu(), xpd.grad
+        err = float((got - want).abs().max() / want.abs().max())
         if err > 1e-4:
             over += 1
-            gap = min(float(((O.power_spectrogram(xp.double(), n, n // 4) - O.power_spectrogram(xt.double(), n, n // 4)).abs()
-                             / O.power_spectrogram(xt.double(), n, n // 4)).min()) for n in ffts)
-            assert gap < 1e-5, f"case {it}: gradient error {err:.2e} without a tie (smallest relative gap {gap:.1e})"
+            ties = _tied_bin_gradients(xp.double(), xt.double(), ffts)
+            assert 1 <= len(ties) <= 6, f"case {it}: gradient error {err:.2e} with {len(ties)} tied bins"
+            best = min(float((got - (want - 2 * sum(sub))).abs().max() / want.abs().max())
+                       for r in range(1, len(ties) + 1) for sub in itertools.combinations(ties, r))
+            print(f"case {it}: err {err:.2e}, {len(ties)} tied bin(s), flip-corrected err {best:.2e}")
+            assert best <= 1e-4, f"case {it}: gradient error {err:.2e}; {best:.2e} after flipping the tied bins"
     assert over <= 3
+
+
+def test_mss_is_bit_reproducible_and_batch_invariant():
+    """No floating-point atomics in the loss (csrc/ddsp_mss.cu): 20 calls give identical loss and gradient bits, and a voice's
+    gradient inside a batch of 4 is bit for bit half its gradient inside a batch of 2 (the means differ by exactly 2)."""
+    from ddsp_pytorch_b200 import ops
+    gen = torch.Generator().manual_seed(5)
+    ffts = [2048, 1024, 512, 256, 128, 64]
+    xp, xt = (torch.randn(4, 16000, generator=gen) * 0.3).cuda(), (torch.randn(4, 16000, generator=gen) * 0.3).cuda()
+
+    def run(p, t):
+        p = p.clone().requires_grad_(True)
+        loss = ops.mss_loss(p, t, ffts)
+        loss.backward()
+        return loss.detach().clone(), p.grad.clone()
+
+    l0, g0 = run(xp, xt)
+    for _ in range(20):
+        l, g = run(xp, xt)
+        assert torch.equal(l, l0) and torch.equal(g, g0)
+    for lo, hi in ((0, 2), (2, 4)):
+        _, gs = run(xp[lo:hi], xt[lo:hi])
+        assert torch.equal(gs, 2 * g0[lo:hi])
+    assert float(g0.abs().max()) > 0
+
+
+@pytest.mark.parametrize("n,overlap,N", [(64, 0.5, 3000), (256, 0.875, 5000), (128, 0.0, 2000), (4, 0.75, 500), (32, 0.6, 1111)])
+def test_mss_other_overlaps_take_the_generic_kernel(n, overlap, N):
+    """hop != n_fft/4 (SSSLoss's `overlap` argument, mss_loss.py:16-21) and n_fft = 4 run the shared-memory kernel whose
+    frames are overlap-added by the gather; same parity bar, same reproducibility."""
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(n + N)
+    xt = torch.randn(2, N, generator=gen) * 0.3
+    xp = 0.5 * xt + torch.randn(2, N, generator=gen) * 0.05
+    xpd = xp.double().requires_grad_(True)
+    want = O.sss_loss(xpd, xt.double(), n, overlap=overlap)
+    want.backward()
+    outs = []
+    for _ in range(2):
+        xc = xp.cuda().requires_grad_(True)
+        got = ops.mss_loss(xc, xt.cuda(), [n], overlap=overlap)
+        got.backward()
+        outs.append((got.detach().clone(), xc.grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert abs(float(got) - float(want)) <= TOL * float(want)
+    assert l2rel(xc.grad, xpd.grad) <= TOL

@@ -68,3 +68,30 @@ def test_package_input_generator_draws_the_oracle_voices():
     want = O.synthetic_controls(3, 7, 5, 4, 16000, 64, seed=9, voice_offset=2)
     got = synthetic_controls(3, 7, 5, 4, 16000, 64, seed=9, voice_offset=2)
     assert all(torch.equal(a, b) for a, b in zip(got, want))
+
+
+def test_work_balanced_shards():
+    """balanced_voice_shards: contiguous cover, nobody empty, bottleneck no worse than the equal-count split and within one
+    voice of the mean; voice_work counts what the kernels evaluate (harmonics at or below sample_rate//2 in either frame of
+    a hop segment) -- checked against the brute-force mask of harmonic_oscillator.py:31."""
+    from ddsp_pytorch_b200.sharding import balanced_voice_shards, voice_shard, voice_work
+    from ddsp_pytorch_b200.synthetic import synthetic_f0
+    B, T, K, sr, hop = 96, 20, 64, 48000, 512
+    f0 = synthetic_f0(B, T, sr, hop, seed=1238)
+    w = voice_work(f0, K, sr, hop, per_sample_cost=0.0)
+    k = torch.arange(1, K + 1, dtype=torch.float32).view(1, 1, -1)
+    kact = ((k * f0) <= float(sr // 2)).sum(-1).double()
+    left, right = torch.cat([kact[:, :1], kact], 1), torch.cat([kact, kact[:, -1:]], 1)
+    n = torch.full((T + 1,), float(hop), dtype=torch.float64)
+    n[0] = n[-1] = hop / 2
+    assert torch.equal(w, (torch.maximum(left, right) * n).sum(1))
+    for world in (1, 2, 3, 8):
+        r = balanced_voice_shards(w.tolist(), world)
+        assert len(r) == world and r[0][0] == 0 and r[-1][1] == B
+        assert all(r[i][1] == r[i + 1][0] for i in range(world - 1)) and all(hi > lo for lo, hi in r)
+        loads = [float(w[lo:hi].sum()) for lo, hi in r]
+        equal = [float(w[slice(*voice_shard(B, world, i))].sum()) for i in range(world)]
+        assert max(loads) <= max(equal) + 1e-9
+        assert max(loads) <= sum(loads) / world + float(w.max())
+    assert balanced_voice_shards([1.0, 1.0], 4) == [(0, 1), (1, 2), (2, 2), (2, 2)]          # fewer voices than ranks: empty tails
+    assert balanced_voice_shards([5.0, 1.0, 1.0, 1.0, 1.0, 1.0], 2) == [(0, 1), (1, 6)]

@@ -1,6 +1,7 @@
 """The training driver's host logic on CPU: 2-rank gloo gradient averaging == single-process full batch, Lightning-layout
-checkpoints, state-dict parity with the reference Decoder.  The synthesis modules are replaced by oracle-backed
-stand-ins through the Decoder's `synth` test hook (the CUDA modules need a GPU; GPU runs are in test_gpu_train.py)."""
+checkpoints, state-dict parity with the reference Decoder.  The CUDA modules need a GPU (GPU runs are in
+test_gpu_train.py), so the model handed to the Trainer here is a twin defined in this file: the package's torch Controller
+with the un-fused tail, and oracle-backed stand-ins for the synthesis modules and the loss."""
 import os
 import socket
 import sys
@@ -65,10 +66,36 @@ class _Loss(nn.Module):
         return O.mss_loss(x_pred, x_true["audio"], [64, 128])
 
 
-def _make(conf, voice_offset):
+class _CpuDecoder(nn.Module):
+    """decoder.py:119-135 with the attribute names of ddsp_pytorch_b200.controller.Decoder."""
+
+    def __init__(self, conf, voice_offset):
+        super().__init__()
+        from ddsp_pytorch_b200.controller import Controller
+        self.controller = Controller(conf, fused_tail=False)
+        self.harmonics, self.noise, self.reverb = _Osc(conf), _Noise(conf, voice_offset), _Reverb(conf)
+
+    def forward(self, z):
+        ctrl = self.controller(z)
+        return self.reverb(self.harmonics(ctrl) + self.noise(ctrl))
+
+
+class _CpuZak(nn.Module):
+    def __init__(self, conf, voice_offset):
+        super().__init__()
+        self.model, self.loss = _CpuDecoder(conf, voice_offset), _Loss()
+
+    def forward(self, batch):
+        return self.model(batch)
+
+    def training_loss(self, batch):
+        return self.loss(self.model(batch), batch)
+
+
+def _make(conf, voice_offset, **kw):
     from ddsp_pytorch_b200.train import Trainer
     torch.manual_seed(0)
-    return Trainer(conf, "cpu", synth=(_Osc(conf), _Noise(conf, voice_offset), _Reverb(conf)), loss=_Loss())
+    return Trainer(conf, "cpu", zak=_CpuZak(conf, voice_offset), **kw)
 
 
 def _grads_after_step(tr, batch):
@@ -120,12 +147,10 @@ def _worker_overlap(rank, world, port, ret):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from ddsp_pytorch_b200.sharding import voice_shard
-        from ddsp_pytorch_b200.train import Trainer, synthetic_batch
+        from ddsp_pytorch_b200.train import synthetic_batch
         conf = small_conf()
         lo, hi = voice_shard(3, world, rank)                         # 2 + 1 voices: unequal shards
-        torch.manual_seed(0)
-        tr = Trainer(conf, "cpu", synth=(_Osc(conf), _Noise(conf, lo), _Reverb(conf)), loss=_Loss(), global_batch=3,
-                     bucket_bytes=1024)
+        tr = _make(conf, lo, global_batch=3, bucket_bytes=1024)
         before = {k: p.detach().clone() for k, p in tr.zak.named_parameters()}
         tr.training_step(synthetic_batch(conf, hi - lo, "cpu", seed=1, voice_offset=lo))
         if rank == 0:
