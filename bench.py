@@ -374,13 +374,13 @@ def run_b200(args):
         barrier()
         my_ems = e0.elapsed_time(e1)
         ems = max_over_ranks(my_ems)
-        per_rank = gather_floats([my_ems / args.steps, float(h2d), float(d2h), float(Bl), -1.0 if numa is None else float(numa)])
+        per_rank = gather_floats([my_ems / args.steps, float(h2d), float(d2h), float(Bl), -2.0 if numa is None else float(numa)])
         e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(sum(r[1] for r in per_rank)), "d2h_bytes_per_step": int(sum(r[2] for r in per_rank)),
                "ms_per_step": ems / args.steps, "chunk_voices": chunk, "chunks_per_rank": -(-Bl // chunk),
                "launches_per_step_rank0": pipe.launches_per_step,
                "per_rank": [{"voices": int(r[3]), "ms_per_step": r[0], "h2d_GBps": r[1] / (r[0] * 1e-3) / 1e9,
-                             "d2h_GBps": r[2] / (r[0] * 1e-3) / 1e9, "numa_node": None if r[4] < 0 else int(r[4])} for r in per_rank],
+                             "d2h_GBps": r[2] / (r[0] * 1e-3) / 1e9, "cpu_binding": "none" if r[4] < -1.5 else ("GPU-local CPUs (NVML mask)" if r[4] < 0 else f"NUMA node {int(r[4])}")} for r in per_rank],
                "result": "synthesised audio y and the gradients of c, a, H (the forward's and the backward's outputs) in pinned host memory",
                "path": "HostSynthPipeline.step: pinned host f0,c,a,H,g -> voice chunks on copy-in / compute / copy-out streams "
                        "(ddsp_noise_forward + ddsp_osc_forward(accumulate) + ddsp_osc_backward + ddsp_noise_backward per chunk) "

@@ -19,29 +19,66 @@ import torch
 from . import _lib
 
 
-def bind_to_gpu_numa_node(device_index: int) -> Optional[int]:
-    """Pin the calling process to the CPUs of the NUMA node the GPU hangs off, so that pinned host buffers allocated
-    afterwards (first touch) are local to the GPU's PCIe root.  Returns the node, or None when sysfs has no answer.
-    Eight ranks that all allocate from the node they happened to start on push every copy of half the GPUs across the
-    socket interconnect."""
+def _gpu_cpu_set(device_index: int):
+    """(numa node or None, set of CPUs local to the GPU): sysfs first, NVML's ideal-CPU mask when the PCI device reports
+    no node (virtual machines)."""
+    props = torch.cuda.get_device_properties(device_index)
     try:
-        bus = torch.cuda.get_device_properties(device_index).pci_bus_id
-        dom = torch.cuda.get_device_properties(device_index).pci_domain_id
-        dev = torch.cuda.get_device_properties(device_index).pci_device_id
-        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        path = f"/sys/bus/pci/devices/{props.pci_domain_id:04x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0/numa_node"
         node = int(open(path).read().strip())
-        if node < 0:
-            return None
-        cpus = set()
-        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
-            lo, _, hi = part.partition("-")
-            cpus.update(range(int(lo), int(hi or lo) + 1))
+        if node >= 0:
+            cpus = set()
+            for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+            return node, cpus
+    except (OSError, ValueError, AttributeError):
+        pass
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(props.uuid)
+            handle = None
+            for i in range(pynvml.nvmlDeviceGetCount()):
+                h = pynvml.nvmlDeviceGetHandleByIndex(i)
+                u = pynvml.nvmlDeviceGetUUID(h)
+                u = u.decode() if isinstance(u, bytes) else u
+                if uuid in u or u.replace("GPU-", "") == uuid:
+                    handle = h
+                    break
+            if handle is None:
+                handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            words = (os.cpu_count() + 63) // 64
+            mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+            cpus = {w * 64 + bit for w, m in enumerate(mask) for bit in range(64) if (int(m) >> bit) & 1}
+            node = None
+            try:
+                nm = pynvml.nvmlDeviceGetMemoryAffinity(handle, 4, pynvml.NVML_AFFINITY_SCOPE_NODE)
+                nodes = [w * 64 + bit for w, m in enumerate(nm) for bit in range(64) if (int(m) >> bit) & 1]
+                node = nodes[0] if nodes else None
+            except Exception:
+                pass
+            return node, cpus
+        finally:
+            pynvml.nvmlShutdown()
+    except Exception:
+        return None, set()
+
+
+def bind_to_gpu_numa_node(device_index: int) -> Optional[int]:
+    """Pin the calling process to the CPUs next to the GPU, so that pinned host buffers allocated afterwards (first touch)
+    are local to the GPU's PCIe root.  Returns the NUMA node (None when it is unknown or nothing was bound).  Eight ranks
+    that all allocate from the node they happened to start on push every copy of half the GPUs across the socket
+    interconnect."""
+    try:
+        node, cpus = _gpu_cpu_set(device_index)
         allowed = cpus & os.sched_getaffinity(0)
         if not allowed:
             return None
         os.sched_setaffinity(0, allowed)
-        return node
-    except (OSError, ValueError, AttributeError, RuntimeError):
+        return node if node is not None else -1
+    except (OSError, RuntimeError, AttributeError):
         return None
 
 
