@@ -10,6 +10,11 @@ contract).  One JSON line per workload:
   ctrl    row X1: fused Controller tail vs the torch expression at cfg 2's shapes
   rtdec   cfg 3 with the Controller in front (RealtimeSynth), eager vs CUDA-graph replay
   rt      cfg 3: OscillatorBank.live + FilteredNoise + Reverb.live_forward per 2048-sample block, p50/p99 latency
+  cfg1    cfg 1 as BASELINE names it (16 kHz, K=100, NB=65, T=125): whole path fwd+bwd
+  rt3p    cfg 3' (64 / 128 / 256-sample blocks, one frame per block)
+  sweep   cfg 4 at K = 100, 128, 180, 256
+  dftgemm north_star item 3: tcgen05 DFT-as-GEMM forward of one scale vs the register-tiled FFT kernel
+  cpu     the reference's CPU path (oracle port) for cfg 1, 1', 5 and cfg 3 p50/p99 -- the cpu_baseline leg of the side rows
 No CPU fallback: needs the CUDA library and a GPU.
 """
 from __future__ import annotations
@@ -96,13 +101,13 @@ def bench_reverb(args, dev):
     return out
 
 
-def bench_path(args, dev):
-    """cfg 1' (shipped config/default.py): decoder tail exactly as decoder.py:129-133 + MSSLoss, fwd+bwd."""
+def bench_path(args, dev, conf=None, T=172, name="cfg1'"):
+    """cfg 1' (shipped config/default.py) or cfg 1 (BASELINE's 16 kHz / K=100 / NB=65): decoder tail exactly as
+    decoder.py:129-133 + MSSLoss, fwd+bwd."""
     import ddsp_pytorch_b200 as d
     from ddsp_pytorch_b200.synthetic import synthetic_controls
-    conf = d.SHIPPED
+    conf = conf or d.SHIPPED
     B, sr, hop, K, NB = 16, conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters
-    T = 172
     N = T * hop
     f0, c, a, H = (t.to(dev) for t in synthetic_controls(B, T, K, NB, sr, hop, seed=1234 + 1))
     target = (torch.randn(B, N, generator=torch.Generator().manual_seed(9)) * 0.1).clamp(-1, 1).to(dev)
@@ -134,16 +139,31 @@ def bench_path(args, dev):
         graph_ms = ev_time(gr.replay, args.reps)
     except Exception as e:                              # report, do not hide: the eager number stands on its own
         graph_ms = f"capture failed: {type(e).__name__}: {e}"[:200]
-    return {"workload": f"cfg1' path: B={B} T={T} sr={sr} K={K} NB={NB}: osc + noise + reverb + 6-scale MSS, fwd+bwd",
+    return {"workload": f"{name} path: B={B} T={T} sr={sr} K={K} NB={NB}: osc + noise + reverb + 6-scale MSS, fwd+bwd",
             "ms": ms, "graph_replay_ms": graph_ms, "samples_per_s": B * N / (ms * 1e-3)}
 
 
-def bench_rt(args, dev):
+def bench_cfg1(args, dev):
+    import ddsp_pytorch_b200 as d
+    return bench_path(args, dev, conf=d.CFG1, T=125, name="cfg1")
+
+
+def bench_rt3p(args, dev):
+    """cfg 3' (BASELINE: 64-256-sample blocks): one frame per block, hop = block size, NB capped at hop/2+1."""
+    import ddsp_pytorch_b200 as d
+    out = []
+    for hop in (64, 128, 256):
+        conf = d.SHIPPED.with_(hop_length=hop, n_noise_filters=min(195, hop // 2 + 1))
+        out.append(bench_rt(args, dev, conf=conf, T=1, name="cfg3'"))
+    return out
+
+
+def bench_rt(args, dev, conf=None, T=4, name="cfg3"):
     """cfg 3 (rt/synth.py:23, autoencoder.py:26-32): one 2048-sample block = 4 frames, batch 1, live path."""
     import ddsp_pytorch_b200 as d
     from ddsp_pytorch_b200.synthetic import synthetic_controls
-    conf = d.SHIPPED
-    sr, hop, K, NB, T = conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters, 4
+    conf = conf or d.SHIPPED
+    sr, hop, K, NB = conf.sample_rate, conf.hop_length, conf.n_harmonics, conf.n_noise_filters
     bank, fn, rv = d.OscillatorBank(conf).to(dev), d.FilteredNoise(conf, seed=7), d.Reverb(conf).to(dev)
     ctrls = []
     for i in range(16):
@@ -167,7 +187,7 @@ def bench_rt(args, dev):
     torch.cuda.synchronize()
     dev_ms = [a.elapsed_time(b) for a, b in evs]
     q = lambda v, p: sorted(v)[min(len(v) - 1, int(p * len(v)))]  # noqa: E731
-    return {"workload": f"cfg3 rt: batch 1, {T * hop}-sample blocks @ {sr} Hz, live osc + noise + live reverb, {n_calls} calls",
+    return {"workload": f"{name} rt: batch 1, {T * hop}-sample blocks @ {sr} Hz, live osc + noise + live reverb, {n_calls} calls",
             "deadline_ms": T * hop / sr * 1e3, "host_p50_ms": q(host_ms, 0.5), "host_p99_ms": q(host_ms, 0.99),
             "host_max_ms": max(host_ms), "device_p50_ms": q(dev_ms, 0.5), "device_p99_ms": q(dev_ms, 0.99),
             "out_shape": list(out.shape)}
@@ -248,18 +268,168 @@ def bench_ctrl(args, dev):
     return out
 
 
+def bench_sweep(args, dev):
+    """cfg 4 over the harmonic counts BASELINE names (K = 100, 128, 180, 256): 1024 voices x 4 s @ 48 kHz, NB = 65, oscillator +
+    filtered noise forward + backward as a CUDA-graph replay (bench.py's step), with the fused-step FP32 roofline per K."""
+    import ddsp_pytorch_b200 as d
+    from ddsp_pytorch_b200 import ops
+    from ddsp_pytorch_b200.sharding import voice_work
+    from ddsp_pytorch_b200.synthetic import synthetic_controls
+    B, T, NB, sr, hop = args.sweep_voices, 375, 65, 48000, 512
+    N = T * hop
+    peak = ops.probe_fp32_fma_tflops()
+    out = []
+    g = torch.randn(B, N, generator=torch.Generator().manual_seed(99)).to(dev)
+    for K in (100, 128, 180, 256):
+        f0, c, a, H = (t.to(dev) for t in synthetic_controls(B, T, K, NB, sr, hop, seed=1234 + 4))
+        c.requires_grad_(True); a.requires_grad_(True); H.requires_grad_(True)
+        calls = torch.zeros(1, dtype=torch.int32, device=dev)
+
+        def body():
+            calls.add_(1)
+            y = ops.filtered_noise(H, hop, seed=7, offset=0, offset_tensor=calls)
+            y = ops.oscillator_bank(f0, c, a, sr, hop, out=y)
+            y.backward(g)
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                c.grad = a.grad = H.grad = None
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        c.grad = a.grad = H.grad = None
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            body()
+        ms = ev_time(gr.replay, args.reps)
+        active = float(voice_work(f0, K, sr, hop, per_sample_cost=0.0).sum())
+        M = 2 * (NB - 1)
+        flop = 18.0 * active + 2.0 * (M + M * NB / hop) * B * N
+        out.append({"workload": f"cfg4 sweep K={K}: {B} voices x 4 s @ {sr} Hz, NB={NB}, osc + noise fwd+bwd (graph replay)",
+                    "ms": ms, "samples_per_s": B * N / (ms * 1e-3), "active_harmonic_samples": active,
+                    "nominal_harmonic_samples": float(B) * N * K, "fused_survey_tflops": flop / (ms * 1e-3) / 1e12,
+                    "fp32_peak_tflops": peak, "fused_frac": flop / (ms * 1e-3) / 1e12 / peak,
+                    "executed_pipe_frac_osc_only": 16.0 * active / (ms * 1e-3) / 1e12 / peak})
+        del gr
+    return out
+
+
+def bench_dftgemm(args, dev):
+    """north_star item 3: the tcgen05 DFT-as-GEMM forward of one scale (csrc/ddsp_dftgemm.cu) against the register-tiled FFT
+    kernel of the product path on the same frames (cfg 5: 64 x 4 s @ 16 kHz), forward only (loss terms, no gradient)."""
+    from ddsp_pytorch_b200 import _lib, ops
+    B, N = 64, 64000
+    g = torch.Generator().manual_seed(1234 + 5)
+    xt = (torch.randn(B, N, generator=g) * 0.1).clamp(-1, 1)
+    xp = (0.5 * xt + torch.randn(B, N, generator=g) * 0.05)
+    xt, xp = xt.to(dev), xp.to(dev)
+    out = []
+    lib = _lib.load()
+    for n in (64, 128):
+        ws = torch.empty(lib.ddsp_dftgemm_workspace_bytes(B, N, n), dtype=torch.uint8, device=dev)
+        fft_ms = ev_time(lambda: ops.mss_loss(xp, xt, [n]), args.reps)
+        prep_ms = ev_time(lambda: ops.dftgemm_sss_terms(xp, xt, n, workspace=ws), args.reps)
+        res = {"workload": f"SSS forward n_fft={n}, {B} x {N} samples ({B * (1 + N // (n // 4))} frames x 2 signals)",
+               "fft_kernel_ms": fft_ms, "dftgemm_prepare_plus_forward_ms": prep_ms}
+        for splits in (3, 1):
+            res[f"dftgemm_forward_{splits}split_ms"] = ev_time(
+                lambda: ops.dftgemm_sss_terms(xp, xt, n, splits=splits, workspace=ws, prepare=False), args.reps)
+        frames = 2.0 * B * (1 + N // (n // 4))
+        res["gemm_flops_3split"] = 6 * 2.0 * frames * n * n
+        res["gemm_tflops_3split"] = res["gemm_flops_3split"] / (res["dftgemm_forward_3split_ms"] * 1e-3) / 1e12
+        ref = ops.mss_loss(xp, xt, [n])
+        t3 = ops.dftgemm_sss_terms(xp, xt, n, workspace=ws)
+        cnt = B * (n // 2 + 1) * (1 + N // (n // 4))
+        res["loss_fft_path"] = float(ref)
+        res["loss_dftgemm_3split"] = float((t3[0] + t3[1]) / cnt)
+        out.append(res)
+    return out
+
+
+def bench_cpu(args, dev):
+    """cpu_baseline leg for the side rows: the oracle port of the reference's torch path in fp32 on all host threads
+    -- cfg 1, cfg 1' and cfg 5 whole (forward + backward), cfg 3 call by call (p50 / p99).  The only place this file touches
+    oracle/; nothing here runs on the GPU."""
+    from oracle import ddsp_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    out = []
+
+    def timed(fn, reps=3):
+        fn()
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t0)
+        return statistics.median(ts) * 1e3
+
+    n_ffts = [2048, 1024, 512, 256, 128, 64]
+    for name, (B, T, K, NB, sr) in (("cfg1", (16, 125, 100, 65, 16000)), ("cfg1'", (16, 172, 180, 195, 44100))):
+        hop = 512
+        f0, c, a, H = O.synthetic_controls(B, T, K, NB, sr, hop, seed=1234 + 1)
+        target = (torch.randn(B, T * hop, generator=torch.Generator().manual_seed(9)) * 0.1).clamp(-1, 1)
+        rn = torch.rand(sr, generator=torch.Generator().manual_seed(3)) * 2 - 1
+
+        def step():
+            cc, aa, HH = (t.detach().requires_grad_(True) for t in (c, a, H))
+            noise, decay, wet = rn.clone().requires_grad_(True), torch.tensor(5.0, requires_grad=True), torch.tensor(0.0, requires_grad=True)
+            u = torch.rand(B, T, hop) * 2 - 1                               # the reference's CPU noise draw (filtered_noise.py:44)
+            y = O.synth_path(f0, cc, aa, HH, u, noise, decay, wet, K, sr, hop)
+            O.mss_loss(y, target, n_ffts).backward()
+
+        ms = timed(step)
+        out.append({"workload": f"CPU {name} path: B={B} T={T} sr={sr} K={K} NB={NB}: osc + noise + reverb + 6-scale MSS, fwd+bwd",
+                    "kind": "port", "cores": torch.get_num_threads(), "ms": ms, "samples_per_s": B * T * hop / (ms * 1e-3)})
+    B, N = 64, 64000
+    g = torch.Generator().manual_seed(1234 + 5)
+    xt = (torch.randn(B, N, generator=g) * 0.1).clamp(-1, 1)
+    xp = (0.5 * xt + torch.randn(B, N, generator=g) * 0.05)
+
+    def mss_step():
+        x = xp.detach().requires_grad_(True)
+        O.mss_loss(x, xt, n_ffts).backward()
+
+    ms = timed(mss_step)
+    out.append({"workload": "CPU cfg5 MSS alone: 64 x 4 s @ 16 kHz, n_fft 2048..64, fwd+bwd", "kind": "port",
+                "cores": torch.get_num_threads(), "ms": ms, "samples_per_s": B * N / (ms * 1e-3)})
+    # cfg 3: live oscillator + noise + live reverb per 2048-sample block, call by call
+    sr, hop, K, NB, T = 44100, 512, 180, 195, 4
+    last, buf = torch.zeros(K), torch.zeros(1, sr)
+    ir = O.reverb_ir(torch.rand(sr) * 2 - 1, torch.tensor(5.0), torch.tensor(0.0), sr)
+    ctrls = [O.synthetic_controls(1, T, K, NB, sr, hop, seed=50 + i) for i in range(16)]
+    lat = []
+    with torch.no_grad():
+        for i in range(20 + args.cpu_rt_calls):
+            f0, c, a, H = ctrls[i % 16]
+            t0 = time.perf_counter()
+            harm, last = O.oscillator_bank_live(f0, c, a, last, K, sr, hop)
+            y, buf = O.reverb_live(buf, harm + O.filtered_noise(H, hop, torch.rand(1, T, hop) * 2 - 1), ir)
+            if i >= 20:
+                lat.append((time.perf_counter() - t0) * 1e3)
+    lat.sort()
+    out.append({"workload": f"CPU cfg3 rt: batch 1, {T * hop}-sample blocks @ {sr} Hz, live osc + noise + live reverb, {len(lat)} calls",
+                "kind": "port", "cores": torch.get_num_threads(), "deadline_ms": T * hop / sr * 1e3, "host_p50_ms": lat[len(lat) // 2],
+                "host_p99_ms": lat[int(0.99 * len(lat))], "host_max_ms": lat[-1]})
+    return out
+
+
 def main():
     p = argparse.ArgumentParser()
     p.add_argument("--workloads", default="mss,reverb,path,rt")
     p.add_argument("--reps", type=int, default=20)
     p.add_argument("--rt-calls", type=int, default=2000)
     p.add_argument("--reverb-big-only", action="store_true", help="reverb: only the B=256 shape (profiling runs)")
+    p.add_argument("--sweep-voices", type=int, default=1024)
+    p.add_argument("--cpu-rt-calls", type=int, default=10000)
     args = p.parse_args()
     if not torch.cuda.is_available():
         raise RuntimeError("bench_extra.py needs a CUDA device; there is no CPU fallback")
     dev = torch.device("cuda", 0)
     torch.manual_seed(0)
-    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt, "ctrl": bench_ctrl, "rtdec": bench_rtdec}
+    table = {"fft": bench_fft, "mss": bench_mss, "reverb": bench_reverb, "path": bench_path, "rt": bench_rt, "ctrl": bench_ctrl, "rtdec": bench_rtdec,
+             "cfg1": bench_cfg1, "rt3p": bench_rt3p, "sweep": bench_sweep, "dftgemm": bench_dftgemm, "cpu": bench_cpu}
     for w in args.workloads.split(","):
         res = table[w](args, dev)
         for r in (res if isinstance(res, list) else [res]):

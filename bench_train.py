@@ -61,6 +61,21 @@ def main():
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1), dev) / args.steps
+    # the same step with the gradient all-reduces switched off: the difference is the collective time the step EXPOSES
+    # (what backward could not hide); measurement only -- the ranks' weights drift apart, so it comes last
+    ms_nocomm = None
+    if world > 1:
+        tr.buckets.skip_collectives = True
+        for _ in range(3):
+            tr.training_step(batch)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            tr.training_step(batch)
+        e1.record()
+        barrier()
+        ms_nocomm = max_over_ranks(e0.elapsed_time(e1), dev) / args.steps
+        tr.buckets.skip_collectives = False
 
     # phase breakdown on rank 0's shard (separate pass, events around each phase)
     def timed(fn, reps=10):
@@ -101,11 +116,9 @@ def main():
         (out["c"].sum() + out["a"].sum() + out["H"].sum()).backward()
         zak.zero_grad(set_to_none=True)
 
-    def comm():
-        for p_ in zak.parameters():
-            if p_.grad is None:
-                p_.grad = torch.zeros_like(p_)
-        allreduce_mean_(list(zak.parameters()))
+    def comm():                 # all buckets reduced back to back with nothing to hide behind
+        tr.buckets.zero(arm=False)
+        tr.buckets.finish()
 
     phases = {"controller_fwd_bwd_ms": timed(controller_fb), "osc_noise_fwd_bwd_ms": timed(synth_fb),
               "reverb_fwd_bwd_ms": timed(reverb_fb), "mss_fwd_bwd_ms": timed(loss_fb), "grad_allreduce_ms": timed(comm)}
@@ -115,6 +128,9 @@ def main():
                                       f"K={conf.n_harmonics}, NB={conf.n_noise_filters}, 6-scale MSS, Adam, amp={args.amp}, graph={args.graph}",
                           "n_gpus": world, "ms_per_step": ms, "samples_per_s": args.global_batch * N / (ms * 1e-3),
                           "loss": float(loss), "trainable_params": n_params, "allreduce_bytes": 4 * n_params,
+                          "ms_per_step_without_allreduce": ms_nocomm,
+                          "allreduce_exposed_ms": None if ms_nocomm is None else ms - ms_nocomm,
+                          "grad_buckets": len(tr.buckets.flats), "collectives_per_step": tr.last_collectives,
                           "phases_rank0": phases}), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -41,6 +41,9 @@ SIGNATURES = {
     "ddsp_mss_scratch_bytes": (_sz, [_p, _p, _i, _i, _i]),
     "ddsp_mss_forward": (_i, [_p, _p, _p, _p, _p, _i, _p, _p, _p, _i, C.c_float, C.c_float, _i, _i, _p]),
     "ddsp_mss_backward": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _p]),
+    "ddsp_dftgemm_workspace_bytes": (_sz, [_i, _i, _i]),
+    "ddsp_dftgemm_prepare": (_i, [_p, _p, _p, _p, _i, _i, _i, _p]),
+    "ddsp_dftgemm_sss_forward": (_i, [_p, _p, _p, _i, _i, C.c_float, _i, _i, _p]),
     "ddsp_rowconv_forward": (_i, [_p, _p, _p, C.c_longlong, _i, _p]),
     "ddsp_rowconv_backward": (_i, [_p, _p, _p, _p, _p, C.c_longlong, _i, _p]),
     "ddsp_ctrl_heads_ldz": (_i, [_i, _i]),

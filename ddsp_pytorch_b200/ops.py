@@ -394,6 +394,34 @@ def mss_loss(x_pred, x_true, n_ffts, alpha: float = 1.0, overlap: float = 0.75, 
     return _MSSLoss.apply(x_pred, x_true, tuple(int(n) for n in n_ffts), tuple(hops), float(alpha), float(eps), tuple(windows))
 
 
+def dftgemm_sss_terms(x_pred: torch.Tensor, x_true: torch.Tensor, n_fft: int, eps: float = 1e-7, splits: int = 3,
+                      window: Optional[torch.Tensor] = None, return_spectra: bool = False, workspace: Optional[torch.Tensor] = None,
+                      prepare: bool = True):
+    """The tcgen05 DFT-as-GEMM experiment (csrc/ddsp_dftgemm.cu): raw sums (sum|Sp-St|, sum|log2 St+eps - log2 Sp+eps|) of one
+    scale, n_fft in {64, 128}, hop = n_fft/4, as a float64 tensor [2]; with return_spectra also the power spectrograms
+    [2, B, F, n_fft/2+1] (true, pred).  Forward only; not on the product path -- `mss_loss` uses the register-tiled FFT."""
+    xp, xt = _f32(x_pred), _f32(x_true)
+    B, N = xp.shape
+    dev = xp.device
+    with torch.cuda.device(dev):
+        lib = _lib.load()
+        nbytes = lib.ddsp_dftgemm_workspace_bytes(B, N, int(n_fft))
+        if nbytes == 0:
+            raise RuntimeError(f"dftgemm_sss_terms: n_fft={n_fft} must be 64 or 128 with n_fft/2 < N={N}")
+        ws = workspace if workspace is not None else _bytes(nbytes, dev)
+        if window is None:
+            window = _torch_hann(int(n_fft), dev)
+        w_ = window.detach().to(device=dev, dtype=torch.float32).contiguous()
+        if prepare:
+            _lib.call("ddsp_dftgemm_prepare", xp.data_ptr(), xt.data_ptr(), w_.data_ptr(), ws.data_ptr(), int(n_fft), B, N, _stream())
+        terms = torch.empty(2, dtype=torch.float64, device=dev)
+        F_ = 1 + N // (int(n_fft) // 4)
+        S = torch.empty(2, B, F_, int(n_fft) // 2 + 1, dtype=torch.float32, device=dev) if return_spectra else None
+        _lib.call("ddsp_dftgemm_sss_forward", ws.data_ptr(), terms.data_ptr(), S.data_ptr() if S is not None else None, int(n_fft),
+                  int(splits), float(eps), B, N, _stream())
+    return (terms, S) if return_spectra else terms
+
+
 class _Rescale(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, hop: int):

@@ -89,6 +89,7 @@ class GradBuckets:
         self.works = []
         self.armed = False
         self.n_collectives = 0
+        self.skip_collectives = False        # measurement only: time a step without its all-reduces (gradients stay local)
         for p in self.params:
             p.register_post_accumulate_grad_hook(self._hook)
 
@@ -117,7 +118,7 @@ class GradBuckets:
         self.pending = [len(ps) for ps in self.members]
         self.launched = [False] * len(self.flats)
         self.works = []
-        self.armed = bool(arm) and self._multi()
+        self.armed = bool(arm) and self._multi() and not self.skip_collectives
 
     def _launch(self, b: int) -> None:
         self.launched[b] = True
@@ -135,7 +136,7 @@ class GradBuckets:
     def finish(self) -> int:
         """After backward: every bucket reduced (those no hook triggered are launched now, in bucket order on all ranks),
         waited for and divided by the world size.  Returns the number of collectives of this step."""
-        if not self._multi():
+        if not self._multi() or self.skip_collectives:
             self.armed = False
             return 0
         for b in range(len(self.flats)):

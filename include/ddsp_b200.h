@@ -196,6 +196,24 @@ int ddsp_mss_backward(const float* gloss, const void* scratch, float* gx_out, co
                       const int* hops_host, int n_scales, int B, int N, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * DFT-as-GEMM variant of ONE scale of the spectral loss on the tcgen05 tensor cores (north_star item 3: "only for the
+ * small FFT sizes where ncu shows it beats a shared-memory radix FFT").  Forward of SSSLoss, mss_loss.py:25-33, for
+ * n_fft in {64, 128}, hop = n_fft/4: frames x windowed real-DFT matrix as a bf16 x 3 split GEMM (TMA-fed operands,
+ * accumulators in TMEM), power spectra and both L1 sums in the epilogue.  Measured against the register-tiled FFT path of
+ * ddsp_mss_forward in profiles/ (DESIGN.md 4.3); the product path (ddsp_mss_forward) does not call it.
+ *   prepare: reflect pad + split of both signals into the workspace's block-row planes, DFT matrix from `window`
+ *            (device fp32 [n_fft] or NULL = periodic Hann);
+ *   forward: terms2 (device double[2]) = sum|Sp-St|, sum|log2(St+eps)-log2(Sp+eps)|  (the two raw sums of loss_terms);
+ *            S_out: NULL, or device float [2][B][F][n_fft/2+1] (true, pred power spectrograms, frame-major) for accuracy
+ *            checks; splits: 3 (six bf16 products, fp32-class accuracy) or 1 (one product, bf16 accuracy).
+ * ------------------------------------------------------------------------------------------ */
+size_t ddsp_dftgemm_workspace_bytes(int B, int N, int n_fft);
+int ddsp_dftgemm_prepare(const float* x_pred, const float* x_true, const float* window, void* workspace,
+                         int n_fft, int B, int N, void* stream);
+int ddsp_dftgemm_sss_forward(void* workspace, double* terms2, float* S_out, int n_fft, int splits, float eps,
+                             int B, int N, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Loudness feature  --  LoudnessEncoder.forward, model/autoencoder/encoder.py:141-156
  *   out[B,F] = mean_k( (20 log10(|STFT(x)[k]| + 1e-20) + a_weight[k]) / 90 + 1 ),  rectangular window,
  *   center=False, F = ddsp_loudness_frames(N, n_fft, hop) = 1 + (N - n_fft)/hop, a_weight [n_fft/2+1] in dB.

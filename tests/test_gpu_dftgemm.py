@@ -1,0 +1,45 @@
+"""The tcgen05 DFT-as-GEMM experiment (csrc/ddsp_dftgemm.cu, north_star item 3) against the fp64 oracle: power spectra and
+the two L1 sums of one scale.  This kernel is measured, not adopted; the test keeps it correct so that
+the measurement means something."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,B,N", [(64, 2, 4000), (64, 3, 64 * 40 + 5), (128, 2, 9000), (128, 1, 16000), (64, 5, 20000)])
+def test_three_split_gemm_matches_the_fp64_spectrogram(n, B, N):
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(n + N)
+    xt = torch.randn(B, N, generator=gen) * 0.1
+    xp = 0.5 * xt + torch.randn(B, N, generator=gen) * 0.05
+    terms, S = ops.dftgemm_sss_terms(xp.cuda(), xt.cuda(), n, splits=3, return_spectra=True)
+    hop = n // 4
+    St = O.power_spectrogram(xt.double(), n, hop).permute(0, 2, 1)          # [B,F,bins]
+    Sp = O.power_spectrogram(xp.double(), n, hop).permute(0, 2, 1)
+    got_t, got_p = S[0].double().cpu(), S[1].double().cpu()
+    assert got_t.shape == St.shape
+    scale = float(St.max())
+    err_abs = max(float((got_t - St).abs().max()), float((got_p - Sp).abs().max())) / scale
+    rel = ((got_p - Sp).abs() / Sp.clamp_min(1e-30))
+    print(f"n={n}: max |S - S64| / max S = {err_abs:.2e};  per-bin relative error: median {float(rel.median()):.2e}, "
+          f"99.9 % {float(rel.flatten().kthvalue(int(0.999 * rel.numel())).values):.2e}, max {float(rel.max()):.2e}")
+    assert err_abs <= 2e-6
+    lin = float((Sp - St).abs().sum())
+    log = float(((St + 1e-7).log2() - (Sp + 1e-7).log2()).abs().sum())
+    assert abs(float(terms[0]) - lin) <= 1e-5 * lin
+    assert abs(float(terms[1]) - log) <= 1e-4 * log
+
+
+def test_single_split_is_bf16_accurate_only():
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    gen = torch.Generator().manual_seed(1)
+    xt = torch.randn(2, 6000, generator=gen) * 0.1
+    xp = 0.5 * xt + torch.randn(2, 6000, generator=gen) * 0.05
+    _, S = ops.dftgemm_sss_terms(xp.cuda(), xt.cuda(), 64, splits=1, return_spectra=True)
+    St = O.power_spectrogram(xt.double(), 64, 16).permute(0, 2, 1)
+    err = float((S[0].double().cpu() - St).abs().max() / St.max())
+    print(f"one bf16 product: max |S - S64| / max S = {err:.2e}")
+    assert 1e-5 < err < 5e-2
