@@ -65,17 +65,21 @@ def main():
     # (what backward could not hide); measurement only -- the ranks' weights drift apart, so it comes last
     ms_nocomm = None
     if world > 1:
-        tr.buckets.skip_collectives = True
-        for _ in range(3):
-            tr.training_step(batch)
+        tr_nc = tr
+        if args.graph:      # a captured step keeps what it captured: time a second trainer whose capture has no collectives
+            torch.manual_seed(0)
+            tr_nc = Trainer(conf, dev, amp=args.amp, noise_seed=7, voice_offset=lo, graph=True)
+        tr_nc.buckets.skip_collectives = True
+        for _ in range(max(3, args.warmup)):
+            tr_nc.training_step(batch)
         barrier()
         e0.record()
         for _ in range(args.steps):
-            tr.training_step(batch)
+            tr_nc.training_step(batch)
         e1.record()
         barrier()
         ms_nocomm = max_over_ranks(e0.elapsed_time(e1), dev) / args.steps
-        tr.buckets.skip_collectives = False
+        tr_nc.buckets.skip_collectives = False
 
     # phase breakdown on rank 0's shard (separate pass, events around each phase)
     def timed(fn, reps=10):
@@ -131,6 +135,7 @@ def main():
                           "ms_per_step_without_allreduce": ms_nocomm,
                           "allreduce_exposed_ms": None if ms_nocomm is None else ms - ms_nocomm,
                           "grad_buckets": len(tr.buckets.flats), "collectives_per_step": tr.last_collectives,
+                          "graph_mode": tr.graph_mode,
                           "phases_rank0": phases}), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -71,7 +71,7 @@ class GradBuckets:
     was not triggered, waits, and divides by the world size.  The CUDA-graph step keeps the hooks disarmed and reduces the
     buckets between its two graphs."""
 
-    def __init__(self, params, bucket_bytes: int = 4 << 20):
+    def __init__(self, params, bucket_bytes: int = 25 << 20):
         self.params = [p for p in params if p.requires_grad]
         self.flats, self.members, self.views = [], [], {}
         cur, size = [], 0
@@ -154,12 +154,21 @@ class GradBuckets:
 class Trainer:
     def __init__(self, conf, device, amp: bool = False, lr: float = 1e-3, noise_seed: Optional[int] = None,
                  voice_offset: int = 0, graph: bool = False, device_counter: Optional[bool] = None,
-                 global_batch: Optional[int] = None, bucket_bytes: int = 4 << 20, zak: Optional[nn.Module] = None):
+                 global_batch: Optional[int] = None, bucket_bytes: int = 25 << 20, zak: Optional[nn.Module] = None,
+                 graph_collectives: bool = True):
         """graph=True: the whole step (forward, backward, gradient all-reduce, Adam) is captured once as a CUDA graph on
         the first call and replayed afterwards (fp32 only; batches are copied into static buffers).
         global_batch: total voices over all ranks; needed only when the ranks' shards differ in size -- the local loss is
         then weighted by B_local * world / global_batch so that the averaged gradient is the full-batch gradient.
-        zak: the module to train (anything with `training_loss(batch)`); default: `Zak(conf, ...)`, the reference's model."""
+        zak: the module to train (anything with `training_loss(batch)`); default: `Zak(conf, ...)`, the reference's model.
+        bucket_bytes: gradient bucket size (stock DDP's 25 MB by default: the 19.9 MB of gradients travel as one all-reduce
+        launched from the last gradient's hook; smaller buckets overlap more of backward but cost a host call each, which
+        an eager step that is already launch-bound on the host cannot afford -- measured on 8 B200: six 4 MB buckets
+        exposed 1.97 ms in a 9.5 ms eager step).
+        graph_collectives: with graph=True on several ranks, capture the bucket all-reduces INSIDE the step's CUDA graph
+        (NCCL's stream forks off the capture at each gradient hook and joins before Adam), so a replay is one launch and
+        the collectives overlap backward; False, or a failed capture, falls back to two graphs with the all-reduces
+        issued eagerly between them."""
         self.device = torch.device(device)
         self.graph = bool(graph) and self.device.type == "cuda" and not amp
         if zak is None:
@@ -177,6 +186,8 @@ class Trainer:
         self.steps = 0
         self.global_batch = global_batch
         self.last_collectives = 0
+        self.graph_collectives = bool(graph_collectives)
+        self.graph_mode = None
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
             for p in self.zak.parameters():             # same initial weights everywhere
                 dist.broadcast(p.data, src=0)
@@ -222,18 +233,44 @@ class Trainer:
                     for v in st.values():
                         if torch.is_tensor(v):
                             v.zero_()
-            # Two graphs with the NCCL all-reduce between them (eager, on the same stream) when there are several ranks;
-            # with one rank the optimizer step is captured into the same graph.
-            self._g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(self._g):
-                self._loss = fwd_bwd()
-                if not multi:
-                    self.opt.step()
             self._g_opt = None
-            if multi:
-                self._g_opt = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(self._g_opt, pool=self._g.pool()):
+            self._g = None
+            if multi and self.graph_collectives:
+                # one graph: forward, backward with the bucket all-reduces launched from the gradient hooks (NCCL's stream is
+                # forked from / joined to the capturing stream by torch's work objects), division, Adam
+                def whole_step():
+                    self.buckets.zero(arm=True)
+                    loss = self.zak.training_loss(self._static)
+                    (loss * weight if weight != 1.0 else loss).backward()
+                    self.buckets.finish()
                     self.opt.step()
+                    return loss.detach()
+                try:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        self._loss = whole_step()
+                    self._g, self.graph_mode = g, "one graph, collectives captured"
+                    self.last_collectives = len(self.buckets.flats)
+                except Exception as e:                  # capture of the collective refused: report it and use two graphs
+                    self.graph_mode = f"two graphs (capture with collectives failed: {type(e).__name__})"
+                    torch.cuda.synchronize(self.device)
+                    self.buckets.works, self.buckets.armed = [], False
+            if self._g is None:
+                # Two graphs with the NCCL all-reduce between them (eager, on the same stream) when there are several ranks;
+                # with one rank the optimizer step is captured into the same graph.
+                self._g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self._g):
+                    self._loss = fwd_bwd()
+                    if not multi:
+                        self.opt.step()
+                if multi:
+                    self._g_opt = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(self._g_opt, pool=self._g.pool()):
+                        self.opt.step()
+                    if self.graph_mode is None:
+                        self.graph_mode = "two graphs, eager collectives between"
+                else:
+                    self.graph_mode = "one graph"
         for k, v in batch.items():
             self._static[k].copy_(v)
         self._g.replay()
