@@ -374,10 +374,23 @@ def run_b200(args):
         barrier()
         my_ems = e0.elapsed_time(e1)
         ems = max_over_ranks(my_ems)
+        # host-link roofline of the same step: the same chunked copies on the same streams with no kernel between them
+        for _ in range(2):
+            pipe.step(*host, *outs, y_out=y_host, copy_only=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            pipe.step(*host, *outs, y_out=y_host, copy_only=True)
+        e1.record()
+        barrier()
+        copy_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
         per_rank = gather_floats([my_ems / args.steps, float(h2d), float(d2h), float(Bl), -2.0 if numa is None else float(numa)])
         e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(sum(r[1] for r in per_rank)), "d2h_bytes_per_step": int(sum(r[2] for r in per_rank)),
-               "ms_per_step": ems / args.steps, "chunk_voices": chunk, "chunks_per_rank": -(-Bl // chunk),
+               "ms_per_step": ems / args.steps, "copy_only_ms_per_step": copy_ms,
+               "frac_of_copy_roofline": copy_ms / (ems / args.steps),
+               "bound": "host link: the step's H2D + D2H copies alone, chunked the same way on the same streams, take copy_only_ms_per_step",
+               "chunk_voices": chunk, "chunks_per_rank": -(-Bl // chunk),
                "launches_per_step_rank0": pipe.launches_per_step,
                "per_rank": [{"voices": int(r[3]), "ms_per_step": r[0], "h2d_GBps": r[1] / (r[0] * 1e-3) / 1e9,
                              "d2h_GBps": r[2] / (r[0] * 1e-3) / 1e9, "cpu_binding": "none" if r[4] < -1.5 else ("GPU-local CPUs (NVML mask)" if r[4] < 0 else f"NUMA node {int(r[4])}")} for r in per_rank],

@@ -119,10 +119,11 @@ class HostSynthPipeline:
         self._key = (C, T)
         return C
 
-    def step(self, f0, c, a, H, g, gc_out, ga_out, gH_out, y_out=None):
+    def step(self, f0, c, a, H, g, gc_out, ga_out, gH_out, y_out=None, copy_only: bool = False):
         """All arguments are PINNED host tensors: f0 [B,T,1], c [B,T,K], a [B,T,1], H [B,T,NB], g [B,N] in; y_out [B,N]
         (optional) receives the synthesised audio, gc_out / ga_out / gH_out receive d sum(g*y)/d c, a, H.  Returns when
-        the host owns the results."""
+        the host owns the results.  copy_only (measurement): the same copies in the same order with no kernel between
+        them -- the host-link roofline of the step."""
         B, T = c.shape[0], c.shape[1]
         if B == 0:
             return
@@ -154,13 +155,14 @@ class HostSynthPipeline:
                         self.s_run.wait_event(out_free[slot])
                     st = self.s_run.cuda_stream
                     voff = (self.voice_offset + lo) & 0xFFFFFFFF
-                    # y = noise(H); y += osc(f0, c, a)  (decoder.py:132), then the two backward passes from g
-                    lib_call("ddsp_noise_forward", P(buf["H"]), None, P(buf["y"]), 0, self.seed, offset, None, voff, n, T, NB, hop, st)
-                    lib_call("ddsp_osc_forward", P(buf["f0"]), P(buf["c"]), P(buf["a"]), P(buf["y"]), P(buf["z"]), P(buf["state"]),
-                             1, n, T, K, hop, sr, st)
-                    lib_call("ddsp_osc_backward", P(buf["g"]), P(buf["f0"]), P(buf["a"]), P(buf["z"]), P(buf["state"]),
-                             P(buf["scratch"]), P(buf["gc"]), P(buf["ga"]), n, T, K, hop, sr, st)
-                    lib_call("ddsp_noise_backward", P(buf["g"]), None, P(buf["gH"]), self.seed, offset, None, voff, n, T, NB, hop, st)
+                    if not copy_only:
+                        # y = noise(H); y += osc(f0, c, a)  (decoder.py:132), then the two backward passes from g
+                        lib_call("ddsp_noise_forward", P(buf["H"]), None, P(buf["y"]), 0, self.seed, offset, None, voff, n, T, NB, hop, st)
+                        lib_call("ddsp_osc_forward", P(buf["f0"]), P(buf["c"]), P(buf["a"]), P(buf["y"]), P(buf["z"]), P(buf["state"]),
+                                 1, n, T, K, hop, sr, st)
+                        lib_call("ddsp_osc_backward", P(buf["g"]), P(buf["f0"]), P(buf["a"]), P(buf["z"]), P(buf["state"]),
+                                 P(buf["scratch"]), P(buf["gc"]), P(buf["ga"]), n, T, K, hop, sr, st)
+                        lib_call("ddsp_noise_backward", P(buf["g"]), None, P(buf["gH"]), self.seed, offset, None, voff, n, T, NB, hop, st)
                     computed = torch.cuda.Event()
                     computed.record(self.s_run)
                     in_free[slot] = computed
