@@ -741,3 +741,40 @@ extern "C" int ddsp_osc_live(const float* f0, const float* c, const float* a, co
     DDSP_CHECK_LAUNCH("osc_live_state_kernel");
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free forward (no counterpart in the reference).
+// Callers that cannot allocate -- code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc --
+// get OscillatorBank.forward with the frame-rate state (ddsp_osc_state_bytes: normalised amplitudes, their sums, active
+// counts, phase prefixes) in a file-scope device array instead of a caller-owned buffer.  Every GPU that loads the
+// library holds the array until exit.  In HOST code `g_osc_noalloc_state` is only a stand-in for the symbol, not a device
+// address: the address is asked for once per device, with that device current, through cudaGetSymbolAddress.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_osc_noalloc_state[DDSP_OSC_NOALLOC_STATE_BYTES];
+
+extern "C" int ddsp_osc_forward_noalloc(const float* f0, const float* c, const float* a, float* y, int accumulate, int B, int T,
+                                        int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_forward_noalloc", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(f0 && c && a && y, "ddsp_osc_forward_noalloc: null pointer argument");
+    const size_t need = ddsp_osc_state_bytes(B, T, K);
+    DDSP_REQUIRE(need <= (size_t)DDSP_OSC_NOALLOC_STATE_BYTES,
+                 "ddsp_osc_forward_noalloc: B=%d T=%d K=%d needs %zu bytes of frame-rate state, the built-in scratch holds %zu "
+                 "(DDSP_OSC_NOALLOC_STATE_BYTES); use ddsp_osc_forward with a caller-owned state buffer",
+                 B, T, K, need, (size_t)DDSP_OSC_NOALLOC_STATE_BYTES);
+    static void* dev_ptr[64] = {nullptr};               // per device: the array lives once in every GPU's copy of the module
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    DDSP_REQUIRE(e == cudaSuccess && dev >= 0 && dev < 64, "ddsp_osc_forward_noalloc: cudaGetDevice failed or device index %d >= 64: %s",
+                 dev, cudaGetErrorString(e));
+    void* state = dev_ptr[dev];
+    if (!state) {
+        e = cudaGetSymbolAddress(&state, g_osc_noalloc_state);          // `dev` is the current device
+        DDSP_REQUIRE(e == cudaSuccess && state, "ddsp_osc_forward_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        dev_ptr[dev] = state;
+    }
+    // prepare writes every byte of the state the synthesis kernel reads (nothing has to start at zero), so the previous
+    // call's contents are simply overwritten -- which is also why two calls that overlap on the GPU would race
+    int rc = ddsp_osc_prepare(f0, c, state, B, T, K, hop, sample_rate, stream);
+    if (rc) return rc;
+    return ddsp_osc_synthesize(f0, a, state, y, nullptr, accumulate, B, T, K, hop, sample_rate, stream);
+}

@@ -76,6 +76,20 @@ int ddsp_osc_grad_segments(const float* g, const float* f0, const float* a, cons
 int ddsp_osc_grad_finalize(const float* f0, const void* state, const void* scratch, float* gc,
                            float* ga, int B, int T, int K, int hop, int sample_rate, void* stream);
 
+/* Allocation-free forward.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * ddsp_osc_forward(..., z_save = NULL, ...), bit for bit, but the frame-rate state lives in a static device array inside
+ * the library (DDSP_OSC_NOALLOC_STATE_BYTES = 8 MiB, held by every GPU that loads the library until exit) instead of a
+ * caller-owned buffer; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   limit: ddsp_osc_state_bytes(B, T, K) <= DDSP_OSC_NOALLOC_STATE_BYTES (e.g. B=16, T=125, K=100, or B=1 real-time
+ *     blocks of any shipped size); larger shapes are rejected with an error message, nothing is launched;
+ *   every call on a device shares the one array: calls that may OVERLAP on the GPU (different streams, or graph replays
+ *     launched concurrently) race -- serialise them; the array keeps the last call's contents and nothing in it has to
+ *     start at zero (the preparation kernel rewrites all of it).  Forward only (no z_save: no backward from this call). */
+#define DDSP_OSC_NOALLOC_STATE_BYTES (8u << 20)
+int ddsp_osc_forward_noalloc(const float* f0, const float* c, const float* a, float* y, int accumulate,
+                             int B, int T, int K, int hop, int sample_rate, void* stream);
+
 /* OscillatorBank.live, harmonic_oscillator.py:64-75: as forward, but voice 0 starts harmonic k from the
  * carried phase last_in[k] (radians; arbitrary per-harmonic values are honoured) and last_out[k] receives
  * the wrapped phase of voice 0's last sample (:72).  last_in and last_out must not alias. */
