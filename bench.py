@@ -46,6 +46,7 @@ def parse_args():
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     p.add_argument("--e2e-chunk", type=int, default=0, help="voices per chunk of the host pipeline (0: about 16 chunks per rank)")
+    p.add_argument("--overlap-noise", action="store_true", help="issue the noise synthesiser on a second stream (its backward then overlaps the oscillator's)")
     p.add_argument("--equal-count-shards", action="store_true", help="shard by voice count instead of by work")
     return p.parse_args()
 
@@ -62,7 +63,7 @@ def workload_config(args, sh, extra=None):
            "noise_bands": sh["NB"], "sample_rate": sh["sr"], "hop": sh["hop"],
            "cache": "per-step working set (c 0.39 GB + g/y/z 0.79 GB each at 1 GPU) exceeds the 126 MB L2; no explicit flush",
            "parallelism": f"voices sharded over {args.gpus} rank(s), no collective",
-           "launch": "eager" if args.no_graph else "CUDA graph replay of the step"}
+           "launch": ("eager" if args.no_graph else "CUDA graph replay of the step") + (", noise synthesiser on a second stream" if args.overlap_noise else "")}
     if extra:
         cfg.update(extra)
     return cfg
@@ -300,10 +301,22 @@ def run_b200(args):
     calls = torch.zeros(1, dtype=torch.int32, device=dev)      # device-side call counter: fresh Philox offset per step
     lib = _lib.load()
 
+    side_noise = torch.cuda.Stream(dev) if args.overlap_noise else None
+
     def step_body():
         """resident inputs -> y = noise(H); y += osc(f0,c,a); backward from g."""
         calls.add_(1)
-        y = ops.filtered_noise(H, hop, seed=seed, offset=0, voice_offset=voff, offset_tensor=calls)
+        if side_noise is not None:
+            # the noise synthesiser on its own stream: autograd runs a node's backward on its forward's stream, so the noise
+            # gradient kernel runs beside the oscillator's gradient kernels and fills their tails
+            cur = torch.cuda.current_stream()
+            side_noise.wait_stream(cur)
+            with torch.cuda.stream(side_noise):
+                y = ops.filtered_noise(H, hop, seed=seed, offset=0, voice_offset=voff, offset_tensor=calls)
+            cur.wait_stream(side_noise)
+            y.record_stream(cur)
+        else:
+            y = ops.filtered_noise(H, hop, seed=seed, offset=0, voice_offset=voff, offset_tensor=calls)
         y = ops.oscillator_bank(f0, c, a, sr, hop, out=y)
         y.backward(g)
         return y

@@ -305,8 +305,8 @@ __global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict_
 // ================================================================================================
 // Fast path (hop % 16 == 0): a TEAM of hop/16 threads owns one frame (one warp at hop = 512), four warps
 // of teams per CTA.  Differences from the generic kernels above:
-//   * noise window in shared memory is padded by 4 floats every 32 (swz) so the stride-16 float4 window
-//     loads of a team are bank-conflict free;
+//   * noise window in shared memory is XOR-swizzled at float4 granularity (swz_f / swz_b below) so the strided float4
+//     window loads of a team are bank-conflict free at every offset;
 //   * 16 outputs x 8 taps register tile: 128 FFMA per 4 LDS.128, three rotating 8-float window chunks
 //     (no register shuffling);
 //   * r = irfft(H) by a cosine recurrence over m per output j (no table look-ups), and only for
@@ -316,7 +316,19 @@ __global__ void __launch_bounds__(512) noise_bwd_kernel(const float* __restrict_
 // ================================================================================================
 constexpr int TEAM_BLOCK = 128;
 
-__device__ __forceinline__ int swz(int i) { return i + ((i >> 5) << 2); }
+// Shared-memory index swizzles of the noise window (float index in, float index out; a float4 stays a float4).
+// An LDS.128 is served a quarter-warp at a time; its 8 lanes are conflict-free when their float4 indices differ mod 8.
+//   forward: lane l reads float4 index 4*l + c (16 outputs per lane).  Unswizzled that is 2 distinct values mod 8.  XOR of
+//     the index with its 32-float row number mod 4 makes the 8 lanes distinct for EVERY c (the lanes touch rows r..r+4 and
+//     rows r, r+4 share a mask, so the misaligned case reduces to the aligned one).  The round-1 layout -- 4 floats of
+//     padding per 32, i.e. a rotation that keeps growing with the row -- collided on rows r and r+4: ncu counted 18 % of
+//     the forward kernel's shared-memory wavefronts as conflicts (profiles/summary_r01g.md).
+//   backward: the 8 lanes of a quarter-warp read float4 index c - 2*tg (tap groups 8 taps apart).  XOR with the row
+//     number mod 2 sends odd rows to the odd float4 slots; any 8 consecutive terms of a stride-2 progression then land in 8
+//     distinct slots (33 % conflicts before).
+// Both permute within an aligned block of 32 floats and leave 32-float-aligned contiguous float4 stores conflict-free.
+__device__ __forceinline__ int swz_f(int i) { return i ^ (((i >> 5) & 3) << 2); }
+__device__ __forceinline__ int swz_b(int i) { return i ^ (((i >> 5) & 1) << 2); }
 
 // A team's shared memory is private to it: when the team is exactly one warp (hop 512) a warp barrier is enough, and the
 // four frames of a CTA drift apart so one frame's FMA-bound convolution overlaps another's latency-bound tap build.
@@ -388,8 +400,8 @@ __device__ __forceinline__ void team_build_r(const float* H, float* rr, int NB, 
 // i.e. even outputs run one tap behind: tap 0 is added before the loop and tap TP (zero) closes the last tile.
 #define NOISE_TILE2(NW, M1, M2, Q0)                                                                             \
     {                                                                                                           \
-        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz(ub - (Q0) - 8));                            \
-        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz(ub - (Q0) - 4));                            \
+        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz_f(ub - (Q0) - 8));                            \
+        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz_f(ub - (Q0) - 4));                            \
         NW[0] = make_float2(l0_.x, l0_.y); NW[1] = make_float2(l0_.z, l0_.w);                                   \
         NW[2] = make_float2(l1_.x, l1_.y); NW[3] = make_float2(l1_.z, l1_.w);                                   \
         const float4 a0_ = *reinterpret_cast<const float4*>(hcA + (Q0));                                        \
@@ -465,7 +477,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
             for (int m = l; m < NB; m += TS) Hs[m] = H[frame * NB + m];
         }
     }
-    for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
+    for (int i = l; i < PADL; i += TS) u[i] = 0.f;           // PADL is a multiple of 32: the swizzle stays inside
     for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
     team_sync(TS);
     if (live) {
@@ -473,7 +485,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
         for (int q = l; q < (hop >> 2); q += TS) {
             const float4 v = nf ? *reinterpret_cast<const float4*>(nf + 4 * q)
                                 : philox_noise4((uint32_t)q, t, voice_offset + b, offset, key);
-            *reinterpret_cast<float4*>(u + swz(PADL + 4 * q)) = v;
+            *reinterpret_cast<float4*>(u + swz_f(PADL + 4 * q)) = v;
             if (4 * q < half) {
                 const float vv[4] = {v.x, v.y, v.z, v.w};
                 for (int e = 0; e < 4; ++e)
@@ -518,8 +530,8 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
         float2 acc2[16];
         float2 wa[4], wb[4], wc[4];
         {
-            const float4 a0 = *reinterpret_cast<const float4*>(u + swz(ub)), a1 = *reinterpret_cast<const float4*>(u + swz(ub + 4));
-            const float4 a2 = *reinterpret_cast<const float4*>(u + swz(ub + 8)), a3 = *reinterpret_cast<const float4*>(u + swz(ub + 12));
+            const float4 a0 = *reinterpret_cast<const float4*>(u + swz_f(ub)), a1 = *reinterpret_cast<const float4*>(u + swz_f(ub + 4));
+            const float4 a2 = *reinterpret_cast<const float4*>(u + swz_f(ub + 8)), a3 = *reinterpret_cast<const float4*>(u + swz_f(ub + 12));
             wb[0] = make_float2(a0.x, a0.y); wb[1] = make_float2(a0.z, a0.w); wb[2] = make_float2(a1.x, a1.y); wb[3] = make_float2(a1.z, a1.w);
             wc[0] = make_float2(a2.x, a2.y); wc[1] = make_float2(a2.z, a2.w); wc[2] = make_float2(a3.x, a3.y); wc[3] = make_float2(a3.z, a3.w);
             const float h0 = h0s[0];                    // tap 0 of the even outputs (they run one tap behind)
@@ -571,13 +583,14 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_fwd_team_kernel(const float*
     team_sync(TS);
     if (live) {
 #pragma unroll
-        for (int r = 0; r < 16; r += 4) *reinterpret_cast<float4*>(outs + 16 * l + r) = make_float4(acc[r], acc[r + 1], acc[r + 2], acc[r + 3]);
+        for (int r = 0; r < 16; r += 4)      // same stride-16 pattern as the window loads: swizzled, or it is a 4-way conflict
+            *reinterpret_cast<float4*>(outs + swz_f(16 * l + r)) = make_float4(acc[r], acc[r + 1], acc[r + 2], acc[r + 3]);
     }
     team_sync(TS);
     if (live) {
         float* yp = y + frame * hop;
         for (int q = l; q < (hop >> 2); q += TS) {
-            float4 o = *reinterpret_cast<const float4*>(outs + 4 * q);
+            float4 o = *reinterpret_cast<const float4*>(outs + swz_f(4 * q));
             if (accumulate) {
                 const float4 p = *reinterpret_cast<const float4*>(yp + 4 * q);
                 o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
@@ -617,8 +630,8 @@ __host__ __device__ inline TeamBwdLayout team_bwd_layout(int NB, int hop) {
 
 #define NOISE_BTILE(LO, UP, JB)                                                                                 \
     {                                                                                                           \
-        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz(PADL + (JB) - q0));                         \
-        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz(PADL + (JB) - q0 + 4));                     \
+        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz_b(PADL + (JB) - q0));                         \
+        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz_b(PADL + (JB) - q0 + 4));                     \
         UP[0] = l0_.x; UP[1] = l0_.y; UP[2] = l0_.z; UP[3] = l0_.w;                                             \
         UP[4] = l1_.x; UP[5] = l1_.y; UP[6] = l1_.z; UP[7] = l1_.w;                                             \
         const float4 g0_ = *reinterpret_cast<const float4*>(gs + (JB));                                         \
@@ -647,7 +660,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
     float* u = gs + hop;                                // swizzled noise, logical index PADL + j
     float* uc = u + L.n_u;                              // uc[half + x] = u[x], x in [-half, half)
     float* g2 = uc + L.n_uc;                            // gradient seen by the wrapped taps
-    float* part = g2 + L.n_g2;                          // [TP][nsl]
+    float* part = g2 + L.n_g2;                          // [nsl][TP], tap index swizzled (swz_b): float4 stores of a tap group
     float* dha = part + L.n_part;
     float* dr = dha + L.n_dha;
     const int half = L.half, PADL = L.PADL, nsl = L.nsl, ntg = L.ntg;
@@ -667,7 +680,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
     }
     const int jw = hop - half;
 
-    for (int i = l; i < swz(PADL); i += TS) u[i] = 0.f;
+    for (int i = l; i < PADL; i += TS) u[i] = 0.f;
     for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
     team_sync(TS);
     if (live) {
@@ -684,7 +697,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
             const float4 v = nf ? *reinterpret_cast<const float4*>(nf + 4 * q)
                                 : philox_noise4((uint32_t)q, t, voice_offset + b, offset, key);
             *reinterpret_cast<float4*>(gs + 4 * q) = gq[it];
-            *reinterpret_cast<float4*>(u + swz(PADL + 4 * q)) = v;
+            *reinterpret_cast<float4*>(u + swz_b(PADL + 4 * q)) = v;
             if (4 * q < half) {
                 const float vv[4] = {v.x, v.y, v.z, v.w};
                 for (int e = 0; e < 4; ++e)
@@ -705,8 +718,8 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
             float wa[8], wb[8];
             const int jb0 = sl * SL;
             {
-                const float4 a0 = *reinterpret_cast<const float4*>(u + swz(PADL + jb0 - q0 - 8));
-                const float4 a1 = *reinterpret_cast<const float4*>(u + swz(PADL + jb0 - q0 - 4));
+                const float4 a0 = *reinterpret_cast<const float4*>(u + swz_b(PADL + jb0 - q0 - 8));
+                const float4 a1 = *reinterpret_cast<const float4*>(u + swz_b(PADL + jb0 - q0 - 4));
                 wa[0] = a0.x; wa[1] = a0.y; wa[2] = a0.z; wa[3] = a0.w; wa[4] = a1.x; wa[5] = a1.y; wa[6] = a1.z; wa[7] = a1.w;
             }
             for (int jb = jb0; jb < jb0 + SL; jb += 16) {
@@ -714,8 +727,10 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
                 if (jb + 8 >= jb0 + SL) break;
                 NOISE_BTILE(wb, wa, jb + 8);
             }
-#pragma unroll
-            for (int d = 0; d < 8; ++d) part[(q0 + d) * nsl + sl] = acc[d];
+            // two float4 per item; the quarter-warp's 8 tap groups land in 8 distinct float4 slots (the [TP][nsl] scalar layout
+            // of round 1 put all 8 on one bank: 64 wavefronts for 8 stores)
+            *reinterpret_cast<float4*>(part + sl * L.TP + swz_b(q0)) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            *reinterpret_cast<float4*>(part + sl * L.TP + swz_b(q0 + 4)) = make_float4(acc[4], acc[5], acc[6], acc[7]);
         }
         // ---- d ha[i] = sum_{j'} g[hop-M/2+j'] u[j'-i] ---------------------------------------------
         // u[jp - i] = 0 for jp < i: start at the pass's first i (team-uniform, multiple of 4 when TS is)
@@ -740,7 +755,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
         for (int p = l; p <= half; p += TS) {
             float v = 0.f;
             if (p < half)
-                for (int i = 0; i < nsl; ++i) v += part[p * nsl + i];
+                for (int i = 0; i < nsl; ++i) v += part[i * L.TP + swz_b(p)];
             if (p >= 1) v += dha[half - p];
             dr[p] = v * (0.5f + 0.5f * cospif((float)p * invh));
         }
