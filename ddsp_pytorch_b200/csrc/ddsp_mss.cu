@@ -521,26 +521,29 @@ struct MssFinishArgs {
     double inv_count[MSS_MAX_SCALES];
 };
 
-__global__ void __launch_bounds__(256) mss_finish_kernel(MssFinishArgs a, double alpha_d, double* __restrict__ terms, float* __restrict__ loss_f32) {
-    __shared__ double sl[256], sq[256];
-    double loss = 0.0;
-    for (int s = 0; s < a.ns; ++s) {
+__global__ void __launch_bounds__(32 * MSS_MAX_SCALES) mss_finish_kernel(MssFinishArgs a, double alpha_d, double* __restrict__ terms,
+                                                                          float* __restrict__ loss_f32) {
+    // one warp per scale: lane-strided sums in a fixed order, xor-shuffle tree (every lane ends with the same bits), then
+    // thread 0 adds the scales in order
+    __shared__ double per_scale[MSS_MAX_SCALES];
+    const int s = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (s < a.ns) {
         double l = 0.0, q = 0.0;
-        for (int i = threadIdx.x; i < a.count[s]; i += 256) { const double2 v = a.part[s][i]; l += v.x; q += v.y; }
-        sl[threadIdx.x] = l; sq[threadIdx.x] = q;
-        __syncthreads();
-        for (int w = 128; w > 0; w >>= 1) {
-            if (threadIdx.x < w) { sl[threadIdx.x] += sl[threadIdx.x + w]; sq[threadIdx.x] += sq[threadIdx.x + w]; }
-            __syncthreads();
+        for (int i = lane; i < a.count[s]; i += 32) { const double2 v = a.part[s][i]; l += v.x; q += v.y; }
+        for (int o = 16; o > 0; o >>= 1) {
+            l += __shfl_xor_sync(0xffffffffu, l, o);
+            q += __shfl_xor_sync(0xffffffffu, q, o);
         }
-        if (threadIdx.x == 0) {
-            terms[1 + 2 * s] = sl[0];
-            terms[2 + 2 * s] = sq[0];
-            loss += (sl[0] + alpha_d * sq[0]) * a.inv_count[s];
+        if (lane == 0) {
+            terms[1 + 2 * s] = l;
+            terms[2 + 2 * s] = q;
+            per_scale[s] = (l + alpha_d * q) * a.inv_count[s];
         }
-        __syncthreads();
     }
+    __syncthreads();
     if (threadIdx.x == 0) {
+        double loss = 0.0;
+        for (int k = 0; k < a.ns; ++k) loss += per_scale[k];
         terms[0] = loss;
         if (loss_f32) loss_f32[0] = (float)loss;
     }
@@ -551,6 +554,7 @@ struct MssCombineScale {
     const float* gs;
     const float* side;
     int fast, n, hop, F, T8, G, SL, items_per_voice;
+    int lh, lt8, lg;          // log2 of n/2, T8 and G (all powers of two on the fast path): the gather divides by shifting
     long long U;
 };
 struct MssCombineArgs {
@@ -558,17 +562,21 @@ struct MssCombineArgs {
     MssCombineScale s[MSS_MAX_SCALES];
 };
 
-// complete gradient mass at extended coordinate u (position u - n/2) of voice b for a fast-path scale
+// complete gradient mass at extended coordinate u (position u - n/2) of voice b for a fast-path scale.  Index arithmetic
+// by shifts and masks: with run-time divisors the six scales cost ~1200 integer instructions per sample and the kernel
+// took 0.2 ms at cfg 5 (profiles/summary_r02.md).
 __device__ __forceinline__ float mss_fast_value(const MssCombineScale& d, int b, long long u) {
-    const int half = d.n >> 1;
     float x = d.gs[(size_t)b * d.U + u];
-    const int p = (int)(u / half), r = (int)(u - (long long)p * half), j = r / d.T8, t = r - j * d.T8, g = p % d.G;
+    const int p = (int)(u >> d.lh), r = (int)u & ((1 << d.lh) - 1), j = r >> d.lt8, t = r & (d.T8 - 1), g = p & (d.G - 1);
+    if (g >= 2 || p == 0) return x;                     // both spill sources are pairs of this item: already summed in the CTA
+    const size_t item_floats = (size_t)d.SL * 6 * d.T8;
+    const float* voice_side = d.side + (size_t)b * d.items_per_voice * item_floats;
     auto side_of = [&](int q) {
-        const int item = q / d.G, slot = d.G >= 2 ? (q % d.G) - (d.G - 2) : 0;
-        return d.side + (((size_t)b * d.items_per_voice + item) * d.SL + slot) * (size_t)(6 * d.T8);
+        const int item = q >> d.lg, slot = d.G >= 2 ? (q & (d.G - 1)) - (d.G - 2) : 0;
+        return voice_side + (size_t)item * item_floats + (size_t)slot * (6 * d.T8);
     };
-    if (g == 0 && p >= 1) x += side_of(p - 1)[j * d.T8 + t];
-    if (j < 2 && g < 2 && p >= 2) x += side_of(p - 2)[(j + 4) * d.T8 + t];
+    if (g == 0) x += side_of(p - 1)[(j << d.lt8) + t];
+    if (j < 2 && p >= 2) x += side_of(p - 2)[((j + 4) << d.lt8) + t];
     return x;
 }
 
@@ -682,7 +690,7 @@ extern "C" int ddsp_mss_forward(const float* x_pred, const float* x_true, double
         fa.count[s] = (int)(pl[s].grid_x * pl[s].grid_y);
         fa.inv_count[s] = pl[s].inv_count;
     }
-    mss_finish_kernel<<<1, 256, 0, st>>>(fa, (double)alpha, loss_terms, loss_f32);
+    mss_finish_kernel<<<1, 32 * n_scales, 0, st>>>(fa, (double)alpha, loss_terms, loss_f32);
     DDSP_CHECK_LAUNCH("mss_finish_kernel");
     return 0;
 }
@@ -704,6 +712,8 @@ extern "C" int ddsp_mss_backward(const float* gloss, const void* scratch, float*
         d.side = reinterpret_cast<const float*>(base + p.off_side);
         d.fast = p.fast; d.n = p.n; d.hop = p.hop; d.F = p.F; d.T8 = p.T8 > 0 ? p.T8 : 1; d.G = p.G > 0 ? p.G : 1; d.SL = p.SL;
         d.items_per_voice = p.items_per_voice; d.U = p.U;
+        auto lg2 = [](int v) { int k = 0; while ((1 << k) < v) ++k; return k; };
+        d.lh = lg2(p.n / 2); d.lt8 = lg2(d.T8); d.lg = lg2(d.G);
     }
     mss_combine_kernel<<<dim3((unsigned)((N + 255) / 256), (unsigned)B), 256, 0, static_cast<cudaStream_t>(stream)>>>(ca, gloss, gx_out, N, 0);
     DDSP_CHECK_LAUNCH("mss_combine_kernel");
