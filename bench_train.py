@@ -137,7 +137,15 @@ def main():
                           "grad_buckets": len(tr.buckets.flats), "collectives_per_step": tr.last_collectives,
                           "graph_mode": tr.graph_mode,
                           "phases_rank0": phases}), flush=True)
+    sys.stdout.flush()
     if world > 1:
+        tr.release_graphs()
+        if ms_nocomm is not None and args.graph:
+            tr_nc.release_graphs()
+        dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+        if args.graph:
+            os._exit(0)         # captured NCCL kernels: do not risk the communicator's teardown path (it hung once at 8 ranks)
         dist.destroy_process_group()
 
 

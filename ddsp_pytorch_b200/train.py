@@ -300,6 +300,17 @@ class Trainer:
         self.steps += 1
         return loss.detach()
 
+    def release_graphs(self) -> None:
+        """Drop the captured CUDA graphs (and with them the NCCL kernels captured inside).  Call before
+        `dist.destroy_process_group()`: tearing the communicator down while a graph still holds its collectives hung the
+        8-rank run at exit."""
+        if torch.cuda.is_available() and self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        self._g = None
+        self._g_opt = None
+        self._static = None
+        self._loss = None
+
     def end_epoch(self, mean_train_loss: float) -> None:
         self.sched.step(mean_train_loss)                # 'monitor': 'train_loss'
 
