@@ -630,37 +630,23 @@ __host__ __device__ inline TeamBwdLayout team_bwd_layout(int NB, int hop) {
     L.n_part = L.TP * nsl;
     L.n_dha = (L.half + 3) & ~3;
     L.n_dr = (L.half + 1 + 3) & ~3;
-    L.total = 2 * hop + L.n_u + L.n_uc + L.n_g2 + L.n_part + L.n_dha + L.n_dr;      // g and its copy shifted by one sample
+    L.total = hop + L.n_u + L.n_uc + L.n_g2 + L.n_part + L.n_dha + L.n_dr;
     return L;
 }
 
-// Packed correlation tile: 8 taps x 8 samples as 32 FFMA2.  Every tap keeps TWO partial sums (the lanes of one float2) so that a
-// sample pair (g[j], g[j+1]) meets an ascending, even-aligned window pair (u[x], u[x+1]):
-//   even tap d : samples (JB+r,   JB+r+1), r = 0,2,4,6  x window pair starting at 8+r-d   -> gradient operand from gs
-//   odd  tap d : samples (JB+r+1, JB+r+2)               x window pair starting at 9+r-d   -> gradient operand from gs1 = gs shifted
-// i.e. odd taps run one sample ahead: over a slice they cover samples [jb0+1, jb0+SL+1).  Summed over the slices that is
-// [1, hop+1): sample 0 meets u[-q0-d] = 0 (left pad) and sample hop reads gs1[hop-1] = 0, so nothing is lost or added.
-// The unpacked tile (64 FFMA per 4 LDS.128) made the backward kernel issue-bound: 1307 FFMA of 2519 warp instructions per
-// frame at 80 % issue-slot utilisation (profiles/summary_r02.md).
-#define NOISE_BTILE2(LO, UP, JB)                                                                                \
+#define NOISE_BTILE(LO, UP, JB)                                                                                 \
     {                                                                                                           \
-        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz_b(PADL + (JB) - q0));                       \
-        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz_b(PADL + (JB) - q0 + 4));                   \
-        UP[0] = make_float2(l0_.x, l0_.y); UP[1] = make_float2(l0_.z, l0_.w);                                   \
-        UP[2] = make_float2(l1_.x, l1_.y); UP[3] = make_float2(l1_.z, l1_.w);                                   \
+        const float4 l0_ = *reinterpret_cast<const float4*>(u + swz_b(PADL + (JB) - q0));                         \
+        const float4 l1_ = *reinterpret_cast<const float4*>(u + swz_b(PADL + (JB) - q0 + 4));                     \
+        UP[0] = l0_.x; UP[1] = l0_.y; UP[2] = l0_.z; UP[3] = l0_.w;                                             \
+        UP[4] = l1_.x; UP[5] = l1_.y; UP[6] = l1_.z; UP[7] = l1_.w;                                             \
         const float4 g0_ = *reinterpret_cast<const float4*>(gs + (JB));                                         \
         const float4 g1_ = *reinterpret_cast<const float4*>(gs + (JB) + 4);                                     \
-        const float4 h0_ = *reinterpret_cast<const float4*>(gs1 + (JB));                                        \
-        const float4 h1_ = *reinterpret_cast<const float4*>(gs1 + (JB) + 4);                                    \
-        const float2 G0_[4] = {make_float2(g0_.x, g0_.y), make_float2(g0_.z, g0_.w), make_float2(g1_.x, g1_.y), \
-                               make_float2(g1_.z, g1_.w)};                                                      \
-        const float2 G1_[4] = {make_float2(h0_.x, h0_.y), make_float2(h0_.z, h0_.w), make_float2(h1_.x, h1_.y), \
-                               make_float2(h1_.z, h1_.w)};                                                      \
-        _Pragma("unroll") for (int d = 0; d < 8; ++d) {                                                         \
-            _Pragma("unroll") for (int rp = 0; rp < 4; ++rp) {                                                  \
-                const int pi = ((d & 1) ? 9 + 2 * rp - d : 8 + 2 * rp - d) >> 1;                                \
-                const float2 wv = pi < 4 ? LO[pi] : UP[pi - 4];                                                 \
-                acc2[d] = __ffma2_rn((d & 1) ? G1_[rp] : G0_[rp], wv, acc2[d]);                                 \
+        const float gv_[8] = {g0_.x, g0_.y, g0_.z, g0_.w, g1_.x, g1_.y, g1_.z, g1_.w};                          \
+        _Pragma("unroll") for (int r = 0; r < 8; ++r) {                                                         \
+            _Pragma("unroll") for (int d = 0; d < 8; ++d) {                                                     \
+                const int ix = 8 + r - d;                                                                       \
+                acc[d] = fmaf(gv_[r], ix < 8 ? LO[ix] : UP[ix - 8], acc[d]);                                    \
             }                                                                                                   \
         }                                                                                                       \
     }
@@ -677,8 +663,7 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
     const int team = threadIdx.x / TS, l = threadIdx.x % TS;
     const TeamBwdLayout L = team_bwd_layout(NB, hop);
     float* gs = smem + (size_t)team * L.total;          // [hop] upstream gradient of the frame
-    float* gs1 = gs + hop;                              // [hop] the same shifted by one sample: gs1[j] = g[j+1], gs1[hop-1] = 0
-    float* u = gs1 + hop;                               // swizzled noise, logical index PADL + j
+    float* u = gs + hop;                                // swizzled noise, logical index PADL + j
     float* uc = u + L.n_u;                              // uc[half + x] = u[x], x in [-half, half)
     float* g2 = uc + L.n_uc;                            // gradient seen by the wrapped taps
     float* part = g2 + L.n_g2;                          // [nsl][TP], tap index swizzled (swz_b): float4 stores of a tap group
@@ -704,12 +689,12 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
     for (int i = l; i < PADL; i += TS) u[i] = 0.f;
     for (int i = l; i < L.n_uc; i += TS) uc[i] = 0.f;
     team_sync(TS);
-    float4 gq[4];                                       // the frame's gradient, 4 float4 per lane (hop/4 float4 over hop/16 lanes)
     if (live) {
         const float* gf = g + frame * hop;
         const float* nf = noise ? noise + frame * hop : nullptr;
-        // the gradient is requested first and parked in registers while the noise is generated; copied load-by-load inside
-        // the loop it cost 13.6 % of the warp samples (ncu r01g)
+        // the frame's gradient is requested first (hop/4 float4 over hop/16 lanes: always 4 per lane) and parked in registers
+        // while the noise is generated; copied load-by-load inside the loop it cost 13.6 % of the warp samples (ncu r01g)
+        float4 gq[4];
 #pragma unroll
         for (int it = 0; it < 4; ++it) gq[it] = *reinterpret_cast<const float4*>(gf + 4 * (l + it * TS));
 #pragma unroll
@@ -728,39 +713,26 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
         for (int i = l; i < L.n_g2; i += TS) g2[i] = i < half ? gf[jw + i] : 0.f;
     }
     team_sync(TS);
-    if (live) {                                         // gs is complete: the shifted copy from the registers + one neighbour
-#pragma unroll
-        for (int it = 0; it < 4; ++it) {
-            const int q = l + it * TS;
-            const float nx = 4 * q + 4 < hop ? gs[4 * q + 4] : 0.f;
-            *reinterpret_cast<float4*>(gs1 + 4 * q) = make_float4(gq[it].y, gq[it].z, gq[it].w, nx);
-        }
-    }
-    team_sync(TS);
     if (live) {
         // ---- d hc[q] = sum_j g[j] u[j-q] ----------------------------------------------------------
         const int SL = hop / nsl;
         for (int w = l; w < ntg * nsl; w += TS) {
             const int sl = w / ntg, tg = w % ntg, q0 = 8 * tg;
-            float2 acc2[8];
+            float acc[8];
 #pragma unroll
-            for (int d = 0; d < 8; ++d) acc2[d] = make_float2(0.f, 0.f);
-            float2 wa[4], wb[4];
+            for (int d = 0; d < 8; ++d) acc[d] = 0.f;
+            float wa[8], wb[8];
             const int jb0 = sl * SL;
             {
                 const float4 a0 = *reinterpret_cast<const float4*>(u + swz_b(PADL + jb0 - q0 - 8));
                 const float4 a1 = *reinterpret_cast<const float4*>(u + swz_b(PADL + jb0 - q0 - 4));
-                wa[0] = make_float2(a0.x, a0.y); wa[1] = make_float2(a0.z, a0.w);
-                wa[2] = make_float2(a1.x, a1.y); wa[3] = make_float2(a1.z, a1.w);
+                wa[0] = a0.x; wa[1] = a0.y; wa[2] = a0.z; wa[3] = a0.w; wa[4] = a1.x; wa[5] = a1.y; wa[6] = a1.z; wa[7] = a1.w;
             }
             for (int jb = jb0; jb < jb0 + SL; jb += 16) {
-                NOISE_BTILE2(wa, wb, jb);
+                NOISE_BTILE(wa, wb, jb);
                 if (jb + 8 >= jb0 + SL) break;
-                NOISE_BTILE2(wb, wa, jb + 8);
+                NOISE_BTILE(wb, wa, jb + 8);
             }
-            float acc[8];
-#pragma unroll
-            for (int d = 0; d < 8; ++d) acc[d] = acc2[d].x + acc2[d].y;
             // two float4 per item; the quarter-warp's 8 tap groups land in 8 distinct float4 slots (the [TP][nsl] scalar layout
             // of round 1 put all 8 on one bank: 64 wavefronts for 8 stores)
             *reinterpret_cast<float4*>(part + sl * L.TP + swz_b(q0)) = make_float4(acc[0], acc[1], acc[2], acc[3]);

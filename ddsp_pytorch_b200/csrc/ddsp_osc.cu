@@ -453,11 +453,15 @@ __global__ void __maxnreg__(RP >= 8 ? 144 : 128) osc_grad_kernel(
         __syncthreads();
         for (int row = tid; row < kn; row += NT) {
             const float4* p4 = reinterpret_cast<const float4*>(&part[row * stride]);
-            float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
+            float2 sa = make_float2(0.f, 0.f), sb = sa;      // packed adds: one issue slot per float2 (the sweep is pure overhead)
+#pragma unroll 8
             for (int c4 = 0; c4 < NT / 2; ++c4) {
                 const float4 v = p4[c4];
-                s0 += v.x; s1 += v.y; t0 += v.z; t1 += v.w;
+                sa = __fadd2_rn(sa, make_float2(v.x, v.y));
+                sb = __fadd2_rn(sb, make_float2(v.z, v.w));
             }
+            float s0 = sa.x, s1 = sa.y;
+            const float t0 = sb.x, t1 = sb.y;
             if (NT & 1) {                                   // odd thread count (tiny hops): last column
                 s0 += part[row * stride + 2 * (NT - 1)];
                 s1 += part[row * stride + 2 * (NT - 1) + 1];
