@@ -63,11 +63,12 @@ _lib = None
 def load() -> C.CDLL:
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("DDSP_B200_LIB", LIB_PATH)     # experiment builds (profiles/probes/variant_bench.py)
+        if not os.path.exists(path):
             raise RuntimeError(
-                f"ddsp_pytorch_b200: {LIB_PATH} is missing. Build it with `python -m ddsp_pytorch_b200.build` "
+                f"ddsp_pytorch_b200: {path} is missing. Build it with `python -m ddsp_pytorch_b200.build` "
                 "(needs nvcc). There is no CPU or eager fallback for this path.")
-        lib = C.CDLL(LIB_PATH)
+        lib = C.CDLL(path)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)          # AttributeError if the library is stale
             fn.restype, fn.argtypes = res, args

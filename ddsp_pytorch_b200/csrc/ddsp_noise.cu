@@ -744,7 +744,6 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
             float a2 = 0.f;
             const float* ux = uc + half - i;
             const int j0 = (i - l) & ~3;
-#pragma unroll 4
             for (int jp = j0; jp < half; jp += 4) {
                 const float4 g4 = *reinterpret_cast<const float4*>(g2 + jp);
                 a2 = fmaf(g4.x, ux[jp], a2);
@@ -777,7 +776,6 @@ __global__ void __launch_bounds__(TEAM_BLOCK) noise_bwd_team_kernel(const float*
             const float dl = -4.f * sh * sh;
             float e = -0.5f * dl, c = 1.f;
             float E = 0.f, O = 0.f;
-#pragma unroll 4
             for (int p4 = 0; p4 <= half; p4 += 4) {
                 const float4 d4 = *reinterpret_cast<const float4*>(dr + p4);
                 const float dv[4] = {d4.x, d4.y, d4.z, d4.w};

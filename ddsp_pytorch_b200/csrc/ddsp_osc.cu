@@ -453,7 +453,8 @@ __global__ void __maxnreg__(RP >= 8 ? 144 : 128) osc_grad_kernel(
         __syncthreads();
         for (int row = tid; row < kn; row += NT) {
             const float4* p4 = reinterpret_cast<const float4*>(&part[row * stride]);
-            float2 sa = make_float2(0.f, 0.f), sb = sa;      // packed adds: one issue slot per float2 (the sweep is pure overhead)
+#ifdef OSC_SWEEP_PACKED                               // measured: 3.757 -> 3.784 ms at cfg 4 (profiles/summary_r02.md); off
+            float2 sa = make_float2(0.f, 0.f), sb = sa;
 #pragma unroll 8
             for (int c4 = 0; c4 < NT / 2; ++c4) {
                 const float4 v = p4[c4];
@@ -462,6 +463,13 @@ __global__ void __maxnreg__(RP >= 8 ? 144 : 128) osc_grad_kernel(
             }
             float s0 = sa.x, s1 = sa.y;
             const float t0 = sb.x, t1 = sb.y;
+#else
+            float s0 = 0.f, s1 = 0.f, t0 = 0.f, t1 = 0.f;
+            for (int c4 = 0; c4 < NT / 2; ++c4) {
+                const float4 v = p4[c4];
+                s0 += v.x; s1 += v.y; t0 += v.z; t1 += v.w;
+            }
+#endif
             if (NT & 1) {                                   // odd thread count (tiny hops): last column
                 s0 += part[row * stride + 2 * (NT - 1)];
                 s1 += part[row * stride + 2 * (NT - 1) + 1];
