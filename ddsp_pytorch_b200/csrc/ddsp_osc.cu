@@ -351,6 +351,133 @@ __global__ void __maxnreg__(RP == 4 ? 72 : (RP >= 8 ? 255 : 128)) osc_synth_kern
 }
 
 // ------------------------------------------------------------------------------------------------
+// d/d f0 (harmonic_oscillator.py:26-43 under autograd: f0 -> k*f0 -> rad/sample -> upsample -> cumsum -> sin).
+// With Theta_n the running phase of the fundamental in cycles, y_n = a_n sum_k c'_k,n sin(2 pi k Theta_n) and
+// d Theta_n / d u_i = 1 for i <= n (u = upsampled f0 / sample_rate), so
+//     dL/du_i = 2 pi * sum_{n >= i} q_n,   q_n = g_n a_n sum_k k c'_k,n cos(2 pi k Theta_n),
+// and dL/df0 is the adjoint of the linear upsampling applied to that reverse running sum, over sample_rate.  The Nyquist
+// mask and the amplitude normalisation do not depend on f0 differentiably (a comparison), exactly as in the reference.
+// osc_dphase_kernel is the synthesis kernel with cosine seeds and amplitudes scaled by the harmonic number; it writes q.
+// ------------------------------------------------------------------------------------------------
+template <int RP>
+__global__ void __maxnreg__(RP == 4 ? 80 : (RP >= 8 ? 255 : 128)) osc_dphase_kernel(
+    const float* __restrict__ cn, const float* __restrict__ a, const int* __restrict__ kact, const SegFix* __restrict__ seg,
+    const float* __restrict__ gup, float* __restrict__ q_out, int T, int K, int hop) {
+    extern __shared__ __align__(16) float4 amp[];      // (k c'_L, k c'_L, k dc', k dc') per active harmonic k
+    constexpr int R = 2 * RP;
+    const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
+    const SegGeom g = seg_geom(s, T, hop);
+    const size_t fL = (size_t)b * T + g.tL, fR = (size_t)b * T + g.tR;
+    const int kmax = max(kact[fL], kact[fR]);
+    const int kpad = (kmax + 1) & ~1;
+    {
+        const float* cl = cn + fL * K;
+        const float* cr = cn + fR * K;
+        for (int k = tid; k < kpad; k += blockDim.x) {
+            float l = 0.f, d = 0.f;
+            if (k < kmax) {
+                const float hk = (float)(k + 1);
+                l = hk * cl[k];
+                d = hk * cr[k] - l;
+            }
+            amp[k] = make_float4(l, l, d, d);
+        }
+    }
+    __syncthreads();
+
+    const int r0 = tid * R;
+    if (r0 >= g.r_hi || r0 + R <= g.r_lo) return;
+
+    float2 cs[RP], dn[RP], dl[RP], sg[RP], Pe[RP], Po[RP], Qe[RP], Qo[RP];
+    seed_pairs<RP>(seg[(size_t)b * (T + 1) + s], r0, cs, dl, sg);       // cs receives sin(theta') here; replaced below
+#pragma unroll
+    for (int j = 0; j < RP; ++j) {
+        dn[j] = make_float2(0.5f * dl[j].x, 0.5f * dl[j].y);            // cos(theta') - cos(0) = delta/2
+        cs[j] = make_float2(1.f + dn[j].x, 1.f + dn[j].y);              // cos(theta') = 1 - 2 sin^2(theta'/2)
+        Pe[j] = Po[j] = Qe[j] = Qo[j] = make_float2(0.f, 0.f);
+    }
+    // the same Reinsch recurrence runs cosines: e_{m+1} = e_m + delta*c_m ; c_{m+1} = c_m + e_{m+1}
+#pragma unroll 2
+    for (int k = 0; k < kpad; k += 2) {
+        const float4 A = amp[k], E = amp[k + 1];
+        const float2 Ac = make_float2(A.x, A.y), Ad = make_float2(A.z, A.w);
+        const float2 Ec = make_float2(E.x, E.y), Ed = make_float2(E.z, E.w);
+#pragma unroll
+        for (int j = 0; j < RP; ++j) {
+            Po[j] = __ffma2_rn(Ac, cs[j], Po[j]);
+            Qo[j] = __ffma2_rn(Ad, cs[j], Qo[j]);
+            dn[j] = __ffma2_rn(dl[j], cs[j], dn[j]);
+            cs[j] = __fadd2_rn(cs[j], dn[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < RP; ++j) {
+            Pe[j] = __ffma2_rn(Ec, cs[j], Pe[j]);
+            Qe[j] = __ffma2_rn(Ed, cs[j], Qe[j]);
+            dn[j] = __ffma2_rn(dl[j], cs[j], dn[j]);
+            cs[j] = __fadd2_rn(cs[j], dn[j]);
+        }
+    }
+    const float aL = a[fL], da = a[fR] - aL;
+    const float inv_hop = 1.0f / (float)hop;
+    const float wb = ((float)r0 + seg_phi(hop)) * inv_hop;
+    const size_t N = (size_t)T * hop;
+    const float* gp = gup + (size_t)b * N + (g.n0 + r0);
+    float* qp = q_out + (size_t)b * N + (g.n0 + r0);
+#pragma unroll
+    for (int j = 0; j < RP; ++j) {
+        const float2 zP = __ffma2_rn(sg[j], Po[j], Pe[j]);              // cos(m theta) = sigma^m cos(m theta')
+        const float2 zQ = __ffma2_rn(sg[j], Qo[j], Qe[j]);
+        const float w0 = fmaf((float)(2 * j), inv_hop, wb), w1 = fmaf((float)(2 * j + 1), inv_hop, wb);
+        const int ra = r0 + 2 * j, rb = ra + 1;
+        if (ra >= g.r_lo && ra < g.r_hi) qp[2 * j] = gp[2 * j] * fmaf(w0, da, aL) * fmaf(w0, zQ.x, zP.x);
+        if (rb >= g.r_lo && rb < g.r_hi) qp[2 * j + 1] = gp[2 * j + 1] * fmaf(w1, da, aL) * fmaf(w1, zQ.y, zP.y);
+    }
+}
+
+// Q[n] = scale * sum_{m >= n} q[m] per voice (fp64 carry and partial sums: N reaches 10^5..10^6 terms), written over q.
+__global__ void __launch_bounds__(256) osc_revscan_kernel(float* __restrict__ q, long long N, double scale) {
+    constexpr int PER = 8, CHUNK = 256 * PER;
+    __shared__ double wsum[8];
+    __shared__ double carry_s;
+    float* qb = q + (size_t)blockIdx.x * N;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry_s = 0.0;
+    __syncthreads();
+    for (long long hi = N; hi > 0; hi -= CHUNK) {
+        // thread t owns the PER samples [hi - (t+1)*PER, hi - t*PER): later samples first
+        const long long top = hi - (long long)tid * PER;
+        double v[PER];
+        double tot = 0.0;
+#pragma unroll
+        for (int e = 0; e < PER; ++e) {
+            const long long idx = top - 1 - e;
+            v[e] = idx >= 0 ? (double)qb[idx] : 0.0;
+            tot += v[e];
+        }
+        double inc = tot;                                   // inclusive scan over threads (thread 0 = latest samples)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+        }
+        if (lane == 31) wsum[wid] = inc;
+        __syncthreads();
+        double before = carry_s;
+        for (int w = 0; w < wid; ++w) before += wsum[w];
+        double run = before + (inc - tot);                  // everything later than this thread's samples
+#pragma unroll
+        for (int e = 0; e < PER; ++e) {
+            const long long idx = top - 1 - e;
+            run += v[e];
+            if (idx >= 0) qb[idx] = (float)(run * scale);
+        }
+        __syncthreads();
+        if (tid == 255) carry_s = run;
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // backward over samples: grid (T+1, B), hop/R threads.
 //   G0[b,s,k] = sum_r g*a_up*sin(k theta),  G1[b,s,k] = sum_r g*a_up*w*sin(k theta)     (segment s)
 //   A0[b,s]   = sum_r g*z,                  A1[b,s]   = sum_r g*z*w
@@ -736,6 +863,43 @@ __global__ void osc_live_state_kernel(const float* __restrict__ f0, const double
 }
 
 }  // namespace ddsp
+
+extern "C" size_t ddsp_osc_backward_f0_scratch_bytes(int B, int T, int hop) {
+    if (B < 1 || T < 1 || hop < 1) return 0;
+    return sizeof(float) * (size_t)B * T * hop;
+}
+
+extern "C" int ddsp_osc_backward_f0(const float* g, const float* f0, const float* a, const void* state, void* scratch, float* gf0,
+                                    int B, int T, int K, int hop, int sample_rate, void* stream) {
+    if (check_osc_shape("ddsp_osc_backward_f0", B, T, K, hop, sample_rate)) return 1;
+    DDSP_REQUIRE(g && f0 && a && state && scratch && gf0, "ddsp_osc_backward_f0: null pointer argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
+    float* q = static_cast<float*>(scratch);
+    const int R = pick_R(hop, 8);
+    const dim3 grid(T + 1, B);
+    const size_t smem = sizeof(float4) * ((K + 1) & ~1);
+#define LAUNCH_DPH(RP)                                                                                                  \
+    do {                                                                                                                \
+        if (smem > 48 * 1024) {                                                                                         \
+            cudaError_t e = cudaFuncSetAttribute(osc_dphase_kernel<RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            DDSP_REQUIRE(e == cudaSuccess, "osc_dphase_kernel: cannot reserve %zu B of shared memory: %s", smem, cudaGetErrorString(e)); \
+        }                                                                                                               \
+        osc_dphase_kernel<RP><<<grid, (hop + 2 * RP - 1) / (2 * RP), smem, st>>>(S.cn, a, S.kact, S.seg, g, q, T, K, hop); \
+    } while (0)
+    switch (R) {
+        case 16: LAUNCH_DPH(8); break;
+        case 8: LAUNCH_DPH(4); break;
+        case 4: LAUNCH_DPH(2); break;
+        default: LAUNCH_DPH(1); break;
+    }
+#undef LAUNCH_DPH
+    DDSP_CHECK_LAUNCH("osc_dphase_kernel");
+    const long long N = (long long)T * hop;
+    osc_revscan_kernel<<<B, 256, 0, st>>>(q, N, 6.283185307179586476925 / (double)sample_rate);
+    DDSP_CHECK_LAUNCH("osc_revscan_kernel");
+    return ddsp_rescale_backward(q, gf0, B, T, 1, hop, stream);       // adjoint of the half-pixel linear upsampling (:52-55)
+}
 
 extern "C" int ddsp_osc_live(const float* f0, const float* c, const float* a, const float* last_in, float* last_out, float* y,
                              void* state, int B, int T, int K, int hop, int sample_rate, void* stream) {

@@ -43,7 +43,7 @@ class _Oscillator(torch.autograd.Function):
         if f0_.numel() != B * T or a_.numel() != B * T:
             raise RuntimeError(f"oscillator: f0 {tuple(f0.shape)} / a {tuple(a.shape)} do not match c {tuple(c.shape)}")
         dev = c_.device
-        need_grad = c.requires_grad or a.requires_grad
+        need_grad = c.requires_grad or a.requires_grad or f0.requires_grad
         accumulate = out is not None
         if accumulate:
             _check_out(out, B, T * hop, dev, "oscillator_bank")
@@ -59,7 +59,7 @@ class _Oscillator(torch.autograd.Function):
         if need_grad:
             ctx.save_for_backward(f0_, a_, z, state)
             ctx.dims = (B, T, K, hop, sample_rate)
-            ctx.shapes = (c.shape, a.shape, c.dtype, a.dtype)
+            ctx.shapes = (c.shape, a.shape, c.dtype, a.dtype, f0.shape, f0.dtype)
         if accumulate:
             ctx.mark_dirty(out)
         return y
@@ -71,18 +71,29 @@ class _Oscillator(torch.autograd.Function):
             return None, None, None, None, None, g_out
         f0_, a_, z, state = ctx.saved_tensors
         B, T, K, hop, sample_rate = ctx.dims
-        c_shape, a_shape, c_dtype, a_dtype = ctx.shapes
+        c_shape, a_shape, c_dtype, a_dtype, f0_shape, f0_dtype = ctx.shapes
         g_ = _f32(g)
         dev = g_.device
+        gc = ga = gf0 = None
         with torch.cuda.device(dev):
             lib = _lib.load()
-            gc = torch.empty(B, T, K, dtype=torch.float32, device=dev)
-            ga = torch.empty(B, T, dtype=torch.float32, device=dev)
-            scratch = _bytes(lib.ddsp_osc_backward_scratch_bytes(B, T, K), dev)
-            _lib.call("ddsp_osc_backward", g_.data_ptr(), f0_.data_ptr(), a_.data_ptr(), z.data_ptr(), state.data_ptr(),
-                      scratch.data_ptr(), gc.data_ptr(), ga.data_ptr(), B, T, K, hop, sample_rate, _stream())
+            if ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
+                gc = torch.empty(B, T, K, dtype=torch.float32, device=dev)
+                ga = torch.empty(B, T, dtype=torch.float32, device=dev)
+                scratch = _bytes(lib.ddsp_osc_backward_scratch_bytes(B, T, K), dev)
+                _lib.call("ddsp_osc_backward", g_.data_ptr(), f0_.data_ptr(), a_.data_ptr(), z.data_ptr(), state.data_ptr(),
+                          scratch.data_ptr(), gc.data_ptr(), ga.data_ptr(), B, T, K, hop, sample_rate, _stream())
+                gc = gc.view(c_shape).to(c_dtype) if ctx.needs_input_grad[1] else None
+                ga = ga.view(a_shape).to(a_dtype) if ctx.needs_input_grad[2] else None
+            if ctx.needs_input_grad[0]:
+                # the reference differentiates through the pitch as well (harmonic_oscillator.py:26-43 is plain autograd)
+                gf0 = torch.empty(B, T, dtype=torch.float32, device=dev)
+                scratch0 = _bytes(lib.ddsp_osc_backward_f0_scratch_bytes(B, T, hop), dev)
+                _lib.call("ddsp_osc_backward_f0", g_.data_ptr(), f0_.data_ptr(), a_.data_ptr(), state.data_ptr(),
+                          scratch0.data_ptr(), gf0.data_ptr(), B, T, K, hop, sample_rate, _stream())
+                gf0 = gf0.view(f0_shape).to(f0_dtype)
         # an accumulated-into `out` passes its gradient straight through to whoever produced it
-        return None, gc.view(c_shape).to(c_dtype), ga.view(a_shape).to(a_dtype), None, None, g_out
+        return gf0, gc, ga, None, None, g_out
 
 
 def oscillator_bank(f0: torch.Tensor, c: torch.Tensor, a: torch.Tensor, sample_rate: int, hop: int,

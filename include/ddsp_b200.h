@@ -68,6 +68,14 @@ int ddsp_osc_backward(const float* g, const float* f0, const float* a, const flo
                       const void* state, void* scratch, float* gc, float* ga, int B, int T, int K,
                       int hop, int sample_rate, void* stream);
 
+/* Gradient of sum(g*y) w.r.t. f0 -> gf0 [B,T] (autograd of :26-43 in the reference: k*f0 -> rad/sample -> upsample ->
+ * cumsum -> sin; the Nyquist comparison carries no gradient there either).  Separate from ddsp_osc_backward because the
+ * training path treats f0 as data; costs about one more synthesis pass.  state: that of the forward call;
+ * scratch: ddsp_osc_backward_f0_scratch_bytes(B, T, hop) bytes (one float per sample). */
+size_t ddsp_osc_backward_f0_scratch_bytes(int B, int T, int hop);
+int ddsp_osc_backward_f0(const float* g, const float* f0, const float* a, const void* state, void* scratch,
+                         float* gf0, int B, int T, int K, int hop, int sample_rate, void* stream);
+
 /* The two launches of ddsp_osc_backward on their own (per-segment sums over samples; frame-rate gather
  * + backward of mask/normalise). */
 int ddsp_osc_grad_segments(const float* g, const float* f0, const float* a, const float* z_save,

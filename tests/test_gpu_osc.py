@@ -11,16 +11,18 @@ WAVE_TOL = 1e-4
 GRAD_TOL = 1e-4
 
 
-def _run(f0, c, a, sr, hop, gup=None):
+def _run(f0, c, a, sr, hop, gup=None, with_f0=False):
     from ddsp_pytorch_b200 import ops
     f0, c, a = (torch.as_tensor(x, dtype=torch.float32).cuda() for x in (f0, c, a))
     c.requires_grad_(gup is not None)
     a.requires_grad_(gup is not None)
+    f0.requires_grad_(gup is not None and with_f0)
     y = ops.oscillator_bank(f0, c, a, sr, hop)
     if gup is None:
         return y.double().cpu()
     (y * torch.as_tensor(gup, dtype=torch.float32).cuda()).sum().backward()
-    return y.detach().double().cpu(), c.grad.double().cpu(), a.grad.double().cpu()
+    out = (y.detach().double().cpu(), c.grad.double().cpu(), a.grad.double().cpu())
+    return out + (f0.grad.double().cpu(),) if with_f0 else out
 
 
 def rel(got, want):
@@ -31,13 +33,17 @@ def rel(got, want):
 @pytest.mark.parametrize("name", ["ref_osc_small.npz", "ref_osc_default.npz", "ref_osc_nyquist.npz", "ref_osc_long.npz"])
 def test_golden_waveform_and_grads(golden, name):
     g = golden(name)
-    y, gc, ga = _run(g["f0"], g["c"], g["a"], int(g["sr"]), int(g["hop"]), g["gup"])
+    y, gc, ga, gf0 = _run(g["f0"], g["c"], g["a"], int(g["sr"]), int(g["hop"]), g["gup"], with_f0=True)
     err = float((y - torch.from_numpy(g["y64"])).abs().max())
     drift = float(np.abs(g["y32"].astype(np.float64) - g["y64"]).max())
     print(f"{name}: |cuda-ref64|={err:.2e}  reference's own |ref32-ref64|={drift:.2e}")
     assert err <= WAVE_TOL
     assert rel(gc, g["gc"]) <= GRAD_TOL
     assert rel(ga, g["ga"]) <= GRAD_TOL
+    # the reference differentiates through the pitch (harmonic_oscillator.py:26-43 under autograd): same bound
+    print(f"{name}: gf0 rel err {rel(gf0, g['gf0']):.2e} (max |gf0| = {float(np.abs(g['gf0']).max()):.3g})")
+    assert gf0.shape == torch.from_numpy(g["gf0"]).shape
+    assert rel(gf0, g["gf0"]) <= GRAD_TOL
 
 
 @pytest.mark.parametrize("B,T,K,sr,hop", [(3, 20, 100, 16000, 512), (2, 9, 180, 44100, 512), (2, 7, 256, 48000, 512),
@@ -55,13 +61,14 @@ def test_against_oracle(B, T, K, sr, hop):
     from oracle import ddsp_oracle as O
     f0, c, a, _ = O.synthetic_controls(B, T, K, 5, sr, hop, seed=100 + K)
     gup = torch.randn(B, T * hop, generator=torch.Generator().manual_seed(K))
-    cd, ad = c.double().requires_grad_(True), a.double().requires_grad_(True)
-    want = O.oscillator_bank(f0.double(), cd, ad, K, sr, hop)
+    cd, ad, fd = c.double().requires_grad_(True), a.double().requires_grad_(True), f0.double().requires_grad_(True)
+    want = O.oscillator_bank(fd, cd, ad, K, sr, hop)
     (want * gup.double()).sum().backward()
-    y, gc, ga = _run(f0, c, a, sr, hop, gup)
+    y, gc, ga, gf0 = _run(f0, c, a, sr, hop, gup, with_f0=True)
     assert float((y - want.detach()).abs().max()) <= WAVE_TOL
     assert rel(gc, cd.grad) <= GRAD_TOL
     assert rel(ga, ad.grad) <= GRAD_TOL
+    assert rel(gf0, fd.grad) <= GRAD_TOL
 
 
 def test_all_masked_frame_gives_nan_like_reference():
@@ -93,6 +100,24 @@ def test_full_size_properties():
     got32 = O.oscillator_bank(f0[:2], c[:2], a[:2], K, sr, hop)
     print(f"full length: |cuda-ref64|={float((y[:2] - want).abs().max()):.2e}  |ref32-ref64|={float((got32.double() - want).abs().max()):.2e}")
     assert float((y[:2] - want).abs().max()) <= WAVE_TOL
+
+
+def test_f0_gradient_alone_and_at_full_length():
+    """Only the pitch requires a gradient (fine-tuning f0 with frozen timbre): no c / a gradient is computed, and one cfg-4
+    sized voice (4 s @ 48 kHz, K = 256: a 192 000-term reverse running sum) stays within the bound of the fp64 oracle."""
+    from ddsp_pytorch_b200 import ops
+    from oracle import ddsp_oracle as O
+    B, T, K, sr, hop = 1, 375, 256, 48000, 512
+    f0, c, a, _ = O.synthetic_controls(B, T, K, 5, sr, hop, seed=41)
+    gup = torch.randn(B, T * hop, generator=torch.Generator().manual_seed(3))
+    fd = f0.double().requires_grad_(True)
+    (O.oscillator_bank(fd, c.double(), a.double(), K, sr, hop) * gup.double()).sum().backward()
+    fc, cc, ac = f0.cuda().requires_grad_(True), c.cuda(), a.cuda()
+    (ops.oscillator_bank(fc, cc, ac, sr, hop) * gup.cuda()).sum().backward()
+    err = rel(fc.grad.double().cpu(), fd.grad)
+    print(f"full-length gf0: rel err {err:.2e}, max |gf0| {float(fd.grad.abs().max()):.3g}")
+    assert fc.grad.shape == f0.shape and cc.grad is None and ac.grad is None
+    assert err <= GRAD_TOL
 
 
 def test_accumulate_into_out():
