@@ -25,6 +25,7 @@ SIGNATURES = {
     "ddsp_osc_backward_scratch_bytes": (_sz, [_i, _i, _i]),
     "ddsp_osc_backward": (_i, [_p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ddsp_osc_forward_noalloc": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "ddsp_osc_tuned_sass": (_i, [_i]),
     "ddsp_osc_backward_f0_scratch_bytes": (_sz, [_i, _i, _i]),
     "ddsp_osc_backward_f0": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ddsp_osc_live": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),

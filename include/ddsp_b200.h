@@ -98,6 +98,14 @@ int ddsp_osc_grad_finalize(const float* f0, const void* state, const void* scrat
 int ddsp_osc_forward_noalloc(const float* f0, const float* c, const float* a, float* y, int accumulate,
                              int B, int T, int K, int hop, int sample_rate, void* stream);
 
+/* No reference counterpart.  The harmonic loops of the two dominant kernels (synthesis with 8 samples per thread, gradient
+ * with 16: every hop that is a multiple of 32, the shipped 512 included) also exist in a hand-scheduled form: the same
+ * instructions in an order that feeds the FMA pipe from the operand reuse cache (ddsp_pytorch_b200/sass_sched.py; results are
+ * bit-identical).  The image is loaded through the driver API on the first oscillator call of a device -- make that call
+ * outside stream capture -- and used from then on.  mode 1 / 0 switches it on (default) / off for the calling process,
+ * any other value only queries; returns bit 0 = synthesis, bit 1 = gradient kernel tuned and in use on the current device. */
+int ddsp_osc_tuned_sass(int mode);
+
 /* OscillatorBank.live, harmonic_oscillator.py:64-75: as forward, but voice 0 starts harmonic k from the
  * carried phase last_in[k] (radians; arbitrary per-harmonic values are honoured) and last_out[k] receives
  * the wrapped phase of voice 0's last sample (:72).  last_in and last_out must not alias. */
