@@ -259,7 +259,9 @@ template <int RP>
 __global__ void __maxnreg__(RP == 4 ? 72 : (RP >= 8 ? 255 : 128)) osc_synth_kernel(
     const float* __restrict__ cn, const float* __restrict__ a, const int* __restrict__ kact,
     const SegFix* __restrict__ seg, float* __restrict__ y, float* __restrict__ z_save, int accumulate, int T, int K, int hop) {
-    extern __shared__ __align__(16) float4 amp[];      // (c'_L, c'_L, dc', dc') per active harmonic: both halves of an FFMA2 operand
+    // (c'_L, dc') per active harmonic.  Each value multiplies BOTH samples of a pair: written as (v, v) the compiler emits the
+    // scalar-broadcast operand form of FFMA2 (R.F32), one register-file read instead of two (sass_sched.py has the arithmetic)
+    extern __shared__ __align__(16) float2 amp2[];
     constexpr int R = 2 * RP;
     const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const SegGeom g = seg_geom(s, T, hop);
@@ -275,7 +277,7 @@ __global__ void __maxnreg__(RP == 4 ? 72 : (RP >= 8 ? 255 : 128)) osc_synth_kern
                 l = cl[k];
                 d = cr[k] - l;
             }
-            amp[k] = make_float4(l, l, d, d);
+            amp2[k] = make_float2(l, d);
         }
     }
     __syncthreads();
@@ -294,9 +296,9 @@ __global__ void __maxnreg__(RP == 4 ? 72 : (RP >= 8 ? 255 : 128)) osc_synth_kern
     // Reinsch recurrence over harmonics m = 1..kmax:  d_{m+1} = d_m + delta*s_m ; s_{m+1} = s_m + d_{m+1}
 #pragma unroll 2
     for (int k = 0; k < kpad; k += 2) {
-        const float4 A = amp[k], E = amp[k + 1];       // odd harmonic k+1, even harmonic k+2
-        const float2 Ac = make_float2(A.x, A.y), Ad = make_float2(A.z, A.w);
-        const float2 Ec = make_float2(E.x, E.y), Ed = make_float2(E.z, E.w);
+        const float4 AE = *reinterpret_cast<const float4*>(amp2 + k);   // odd harmonic k+1, even harmonic k+2
+        const float2 Ac = make_float2(AE.x, AE.x), Ad = make_float2(AE.y, AE.y);
+        const float2 Ec = make_float2(AE.z, AE.z), Ed = make_float2(AE.w, AE.w);
 #pragma unroll
         for (int j = 0; j < RP; ++j) {
             Po[j] = __ffma2_rn(Ac, sn[j], Po[j]);
@@ -811,7 +813,7 @@ extern "C" int ddsp_osc_synthesize(const float* f0, const float* a, const void* 
     const OscState S = carve_osc_state(const_cast<void*>(state), B, T, K);
     const int R = pick_R(hop, 8);                      // 16 samples per thread measured 2 % slower here (one barrier only)
     const dim3 grid(T + 1, B);
-    const size_t smem = sizeof(float4) * ((K + 1) & ~1);
+    const size_t smem = sizeof(float2) * ((K + 1) & ~1);
 #define LAUNCH_SYNTH(RP) \
     osc_synth_kernel<RP><<<grid, (hop + 2 * RP - 1) / (2 * RP), smem, st>>>(S.cn, a, S.kact, S.seg, y, z_save, accumulate, T, K, hop)
     if (smem > 48 * 1024) {
