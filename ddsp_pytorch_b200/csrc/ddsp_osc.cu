@@ -704,7 +704,10 @@ using namespace ddsp;
 // ------------------------------------------------------------------------------------------------
 #ifdef DDSP_HAVE_TUNED
 #include <cuda.h>
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
+#include <vector>
 #include "ddsp_osc_tuned.inc"      // kTunedCubin[], kTunedSynth4[], kTunedGrad8[] (mangled names, "" when not tuned)
 namespace {
 struct DriverApi {
@@ -745,7 +748,20 @@ TunedDevice* tuned_kernels() {
                 g_drv.ok = drv_entry("cuModuleLoadData", g_drv.moduleLoadData) && drv_entry("cuModuleGetFunction", g_drv.moduleGetFunction) &&
                            drv_entry("cuFuncSetAttribute", g_drv.funcSetAttribute) && drv_entry("cuLaunchKernel", g_drv.launchKernel);
             CUmodule mod = nullptr;
-            if (g_drv.ok && cudaFree(nullptr) == cudaSuccess && g_drv.moduleLoadData(&mod, kTunedCubin) == CUDA_SUCCESS) {
+            const void* image = kTunedCubin;
+            // scheduler experiments (profiles/probes/sass_variants.py): DDSP_B200_TUNED_CUBIN=<file> replaces the embedded image
+            static std::vector<char> file_image;
+            if (const char* path = getenv("DDSP_B200_TUNED_CUBIN")) {
+                if (FILE* fp = fopen(path, "rb")) {
+                    fseek(fp, 0, SEEK_END);
+                    const long n = ftell(fp);
+                    fseek(fp, 0, SEEK_SET);
+                    file_image.resize(n > 0 ? n : 0);
+                    if (n > 0 && fread(file_image.data(), 1, n, fp) == (size_t)n) image = file_image.data();
+                    fclose(fp);
+                }
+            }
+            if (g_drv.ok && cudaFree(nullptr) == cudaSuccess && g_drv.moduleLoadData(&mod, image) == CUDA_SUCCESS) {
                 t.synth4 = t.grad8 = nullptr;
                 if (kTunedSynth4[0] && g_drv.moduleGetFunction(&t.synth4, mod, kTunedSynth4) != CUDA_SUCCESS) t.synth4 = nullptr;
                 if (kTunedGrad8[0] && g_drv.moduleGetFunction(&t.grad8, mod, kTunedGrad8) != CUDA_SUCCESS) t.grad8 = nullptr;
