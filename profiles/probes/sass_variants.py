@@ -8,7 +8,8 @@ VARIANTS = {"lat6": {"lat": 6}, "lat6_ygroup": {"lat": 6, "yield": "group"}, "la
             "lat6_order_ygroup": {"lat": 6, "key": "order", "yield": "group"}, "lat8": {"lat": 8}, "lat8_ygroup": {"lat": 8, "yield": "group"},
             "lat5": {"lat": 5}, "lat7": {"lat": 7}, "lat10": {"lat": 10}}
 if len(sys.argv) > 1 and sys.argv[1] == "run":
-    for name in VARIANTS:
+    import glob
+    for name in sorted(os.path.basename(f)[:-6] for f in glob.glob(os.path.join(OUT, "*.cubin"))):
         env = dict(os.environ, DDSP_B200_TUNED_CUBIN=os.path.join(OUT, name + ".cubin"))
         r = subprocess.run([sys.executable, os.path.join(ROOT, "profiles", "probes", "tuned_sass_bench.py"), "1024", "once"], env=env, capture_output=True, text=True)
         print(name, [l for l in r.stdout.splitlines() if l.startswith("mode 1")][:1], r.stderr[-200:] if r.returncode else "")
