@@ -60,3 +60,43 @@ def test_bits_equal_under_load_and_over_repeats():
         assert have == 3
         for x, y in zip(tuned, stock):
             assert torch.equal(x, y)
+
+
+def test_tuned_kernels_inside_a_cuda_graph():
+    """the driver-API launches are captured like any other: a replayed step equals the eager step of the stock kernels"""
+    from ddsp_pytorch_b200 import _lib, ops
+    lib = _lib.load()
+    B, T, K, sr, hop = 4, 50, 100, 16000, 512
+    g = torch.Generator(device="cuda").manual_seed(5)
+    f0 = 100.0 + 500.0 * torch.rand(B, T, device="cuda", generator=g)
+    c = torch.rand(B, T, K, device="cuda", generator=g).requires_grad_(True)
+    a = torch.rand(B, T, device="cuda", generator=g).requires_grad_(True)
+    gup = torch.randn(B, T * hop, device="cuda", generator=g)
+
+    def step():
+        c.grad = None
+        a.grad = None
+        y = ops.oscillator_bank(f0, c, a, sr, hop)
+        y.backward(gup)
+        return y.detach(), c.grad, a.grad
+
+    assert lib.ddsp_osc_tuned_sass(1) == 3
+    step()                                              # loads the image outside capture
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            out = step()
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    replayed = [t.clone() for t in out]
+    try:
+        lib.ddsp_osc_tuned_sass(0)
+        stock = [t.clone() for t in step()]
+    finally:
+        lib.ddsp_osc_tuned_sass(1)
+    for x, y in zip(replayed, stock):
+        assert torch.equal(x, y)
