@@ -27,6 +27,7 @@ def main():
     p.add_argument("--global-batch", type=int, default=32)
     p.add_argument("--amp", action="store_true", help="fp16 autocast of the Controller (reference: precision=16)")
     p.add_argument("--graph", action="store_true", help="capture the whole training step as a CUDA graph and replay it")
+    p.add_argument("--gpus", type=int, default=None, help="accepted for symmetry with bench.py; the world size comes from torchrun")
     args = p.parse_args()
     import ddsp_pytorch_b200 as d
     from ddsp_pytorch_b200.sharding import max_over_ranks, voice_shard
