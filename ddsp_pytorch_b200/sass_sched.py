@@ -31,7 +31,7 @@ import subprocess
 PACKED = ("FFMA2", "FADD2", "FMUL2")
 FP = PACKED + ("FFMA", "FADD", "FMUL")
 FMA_PIPE = FP + ("IMAD",)
-KNOWN = FP + ("IMAD", "LEA", "IADD3", "MOV", "LDS", "STS", "UIADD3", "UISETP", "UMOV", "ULEA", "BRA", "NOP", "ISETP", "LOP3")
+KNOWN = FP + ("IMAD", "LEA", "IADD3", "MOV", "LDS", "STS", "UIADD3", "UISETP", "UMOV", "ULEA", "BRA", "NOP", "ISETP", "LOP3", "SHF")
 FP_LATENCY = 6          # ptxas itself goes down to 4; 6 measured faster on the gradient loop (profiles/summary_r02.md)
 # experiment knobs (profiles/probes/sass_variants.py); the defaults are what build.py ships
 OPTS = {"yield": "group", "key": "default"}
@@ -186,8 +186,11 @@ def _find_block(il):
         targets.append((ins["addr"], tgt))
         if tgt < ins["addr"]:
             lo = next(i for i, x in enumerate(il) if x["addr"] == tgt)
-            n = sum(1 for x in il[lo:idx + 1] if x["text"].split()[0].split(".")[0] in PACKED)
-            if best is None or n > best[0]:
+            n = sum((2 if b_ in PACKED else 1) for b_ in (re.sub(r"^@!?U?P\d+\s+", "", x["text"]).split()[0].split(".")[0]
+                                                            for x in il[lo:idx + 1]) if b_ in FP)
+            straight = not any(re.sub(r"^@!?U?P\d+\s+", "", x["text"]).split()[0].split(".")[0] in
+                               ("BRA", "BSSY", "BSYNC", "BAR", "EXIT", "CALL", "RET", "WARPSYNC", "BREAK") for x in il[lo:idx])
+            if straight and (best is None or n > best[0]):
                 best = (n, lo, idx)
     if best is None:
         return None
@@ -364,8 +367,13 @@ def schedule_block(block, entry_ready=None, entry_waits=None, log=None):
         for x in block:
             x["reuse_old"] = x["ctl"]["reuse"]
         npk = sum(1 for x in block if x["packed"])
-        log.append("%d packed instructions, register-file cycles per packed instruction %.3f -> %.3f, issue time of the block %d -> %d cycles" % (
-            npk, cost(block, "reuse_old") / npk, cost(new, "reuse_new") / npk, t_orig[-1] + block[-1]["ctl"]["stall"], total))
+        if npk:
+            log.append("%d packed instructions, register-file cycles per packed instruction %.3f -> %.3f, issue time of the block %d -> %d cycles" % (
+                npk, cost(block, "reuse_old") / npk, cost(new, "reuse_new") / npk, t_orig[-1] + block[-1]["ctl"]["stall"], total))
+        else:
+            nfp = sum(1 for x in block if x["fp"])
+            log.append("%d FP instructions, register-file cycles per instruction %.3f -> %.3f, issue time of the block %d -> %d cycles" % (
+                nfp, cost(block, "reuse_old") / nfp, cost(new, "reuse_new") / nfp, t_orig[-1] + block[-1]["ctl"]["stall"], total))
     return new, None
 
 
