@@ -1,6 +1,7 @@
 // Library-wide pieces of the C ABI: version, per-thread error text, FP32 peak probe.
 #include <stdarg.h>
 #include <atomic>
+#include <mutex>
 #include "ddsp_common.cuh"
 
 namespace ddsp {
@@ -32,7 +33,119 @@ __global__ void __launch_bounds__(1024) fma_probe_kernel(float* out, int iters) 
 }
 }  // namespace ddsp
 
+#ifdef DDSP_HAVE_TUNED
+#include <cstdio>
+#include <cstdlib>
+#include "ddsp_tuned.cuh"
+namespace ddsp {
+namespace {
+struct DriverApi {
+    CUresult (*moduleLoadData)(CUmodule*, const void*);
+    CUresult (*moduleGetFunction)(CUfunction*, CUmodule, const char*);
+    CUresult (*funcSetAttribute)(CUfunction, CUfunction_attribute, int);
+    CUresult (*launchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream, void**, void**);
+    int state;                    // 0 not resolved, 1 ok, -1 missing
+};
+DriverApi g_drv = {};
+std::mutex g_drv_lock;
+std::atomic<int> g_tuned_on{1};
+
+template <class F> bool drv_entry(const char* name, F& fn) {      // through the runtime: no link-time dependency on libcuda
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess || !p) return false;
+    fn = reinterpret_cast<F>(p);
+    return true;
+}
+
+bool driver_ready() {
+    if (g_drv.state == 0) {
+        std::lock_guard<std::mutex> lock(g_drv_lock);
+        if (g_drv.state == 0)
+            g_drv.state = (drv_entry("cuModuleLoadData", g_drv.moduleLoadData) && drv_entry("cuModuleGetFunction", g_drv.moduleGetFunction) &&
+                           drv_entry("cuFuncSetAttribute", g_drv.funcSetAttribute) && drv_entry("cuLaunchKernel", g_drv.launchKernel)) ? 1 : -1;
+    }
+    return g_drv.state == 1;
+}
+}  // namespace
+
+void tuned_enable(int on) { g_tuned_on.store(on ? 1 : 0, std::memory_order_relaxed); }
+int tuned_enabled() { return g_tuned_on.load(std::memory_order_relaxed); }
+
+CUfunction tuned_function(TunedImage& img, TunedKernel& k) {
+    if (!tuned_enabled() || !k.name || !k.name[0]) return nullptr;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= TUNED_MAX_DEVICES) return nullptr;
+    if (k.state[dev] == 0 || img.state[dev] == 0) {
+        std::lock_guard<std::mutex> lock(img.lock);
+        if (img.state[dev] == 0) {
+            int st = -1;
+            const void* image = img.image;
+            if (const char* path = img.env ? getenv(img.env) : nullptr) {
+                if (FILE* fp = fopen(path, "rb")) {
+                    fseek(fp, 0, SEEK_END);
+                    const long n = ftell(fp);
+                    fseek(fp, 0, SEEK_SET);
+                    img.file.resize(n > 0 ? n : 0);
+                    if (n > 0 && fread(img.file.data(), 1, n, fp) == (size_t)n) image = img.file.data();
+                    fclose(fp);
+                }
+            }
+            CUmodule mod = nullptr;
+            if (driver_ready() && cudaFree(nullptr) == cudaSuccess && g_drv.moduleLoadData(&mod, image) == CUDA_SUCCESS) {
+                img.module[dev] = mod;
+                st = 1;
+            }
+            cudaGetLastError();
+            img.state[dev] = st;
+        }
+        if (k.state[dev] == 0) {
+            CUfunction f = nullptr;
+            k.fn[dev] = (img.state[dev] == 1 && g_drv.moduleGetFunction(&f, img.module[dev], k.name) == CUDA_SUCCESS) ? f : nullptr;
+            k.state[dev] = k.fn[dev] ? 1 : -1;
+        }
+    }
+    return k.state[dev] == 1 ? k.fn[dev] : nullptr;
+}
+
+int tuned_launch(CUfunction f, dim3 grid, unsigned threads, size_t smem, cudaStream_t st, void** params, const char* what) {
+    if (smem > 48 * 1024) {
+        CUresult r = g_drv.funcSetAttribute(f, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
+        if (r == CUDA_ERROR_INVALID_CONTEXT) {
+            cudaFree(nullptr);
+            r = g_drv.funcSetAttribute(f, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
+        }
+        DDSP_REQUIRE(r == CUDA_SUCCESS, "%s: cannot reserve %zu B of shared memory (driver error %d)", what, smem, (int)r);
+    }
+    CUresult r = g_drv.launchKernel(f, grid.x, grid.y, grid.z, threads, 1, 1, (unsigned)smem, st, params, nullptr);
+    if (r == CUDA_ERROR_INVALID_CONTEXT) {
+        // a thread that has made no runtime call yet (an autograd worker served from the caching allocator) has no current
+        // context for the driver API: bind the device's primary context the way the runtime does, then launch again
+        cudaFree(nullptr);
+        r = g_drv.launchKernel(f, grid.x, grid.y, grid.z, threads, 1, 1, (unsigned)smem, st, params, nullptr);
+    }
+    count_launch();
+    DDSP_REQUIRE(r == CUDA_SUCCESS, "%s: launch failed (driver error %d)", what, (int)r);
+    return 0;
+}
+}  // namespace ddsp
+#endif
+
+namespace ddsp {
+int osc_tuned_mask();        // ddsp_osc.cu: bit 0 synthesis, bit 1 gradient kernel available from the hand-scheduled image
+}
+
 using namespace ddsp;
+
+extern "C" int ddsp_osc_tuned_sass(int mode) {
+#ifdef DDSP_HAVE_TUNED
+    if (mode == 0 || mode == 1) tuned_enable(mode);
+    return tuned_enabled() ? osc_tuned_mask() : 0;
+#else
+    (void)mode;
+    return 0;
+#endif
+}
 
 extern "C" int ddsp_abi_version(void) { return DDSP_B200_ABI_VERSION; }
 

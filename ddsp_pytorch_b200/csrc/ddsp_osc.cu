@@ -703,100 +703,23 @@ using namespace ddsp;
 // ones; if anything is missing (no tuned image in this build, load refused) the stock kernels run.
 // ------------------------------------------------------------------------------------------------
 #ifdef DDSP_HAVE_TUNED
-#include <cuda.h>
-#include <cstdio>
-#include <cstdlib>
-#include <mutex>
-#include <vector>
+#include "ddsp_tuned.cuh"
 #include "ddsp_osc_tuned.inc"      // kTunedCubin[], kTunedSynth4[], kTunedGrad8[] (mangled names, "" when not tuned)
 namespace {
-struct DriverApi {
-    CUresult (*moduleLoadData)(CUmodule*, const void*);
-    CUresult (*moduleGetFunction)(CUfunction*, CUmodule, const char*);
-    CUresult (*funcSetAttribute)(CUfunction, CUfunction_attribute, int);
-    CUresult (*launchKernel)(CUfunction, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, unsigned, CUstream, void**, void**);
-    bool ok;
-};
-struct TunedDevice {
-    int state;                    // 0 not tried, 1 loaded, -1 unavailable
-    CUfunction synth4, grad8;
-};
-DriverApi g_drv = {};
-TunedDevice g_tuned[64] = {};
-std::mutex g_tuned_mutex;
-std::atomic<int> g_tuned_enabled{1};
-
-template <class F> bool drv_entry(const char* name, F& fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess || !p) return false;
-    fn = reinterpret_cast<F>(p);
-    return true;
-}
-
-// the tuned kernels of the current device, or nullptr.  First use loads the image: call once outside stream capture.
-TunedDevice* tuned_kernels() {
-    if (!g_tuned_enabled.load(std::memory_order_relaxed)) return nullptr;
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    TunedDevice& t = g_tuned[dev];
-    if (t.state == 0) {
-        std::lock_guard<std::mutex> lock(g_tuned_mutex);
-        if (t.state == 0) {
-            int st = -1;
-            if (!g_drv.ok)
-                g_drv.ok = drv_entry("cuModuleLoadData", g_drv.moduleLoadData) && drv_entry("cuModuleGetFunction", g_drv.moduleGetFunction) &&
-                           drv_entry("cuFuncSetAttribute", g_drv.funcSetAttribute) && drv_entry("cuLaunchKernel", g_drv.launchKernel);
-            CUmodule mod = nullptr;
-            const void* image = kTunedCubin;
-            // scheduler experiments (profiles/probes/sass_variants.py): DDSP_B200_TUNED_CUBIN=<file> replaces the embedded image
-            static std::vector<char> file_image;
-            if (const char* path = getenv("DDSP_B200_TUNED_CUBIN")) {
-                if (FILE* fp = fopen(path, "rb")) {
-                    fseek(fp, 0, SEEK_END);
-                    const long n = ftell(fp);
-                    fseek(fp, 0, SEEK_SET);
-                    file_image.resize(n > 0 ? n : 0);
-                    if (n > 0 && fread(file_image.data(), 1, n, fp) == (size_t)n) image = file_image.data();
-                    fclose(fp);
-                }
-            }
-            if (g_drv.ok && cudaFree(nullptr) == cudaSuccess && g_drv.moduleLoadData(&mod, image) == CUDA_SUCCESS) {
-                t.synth4 = t.grad8 = nullptr;
-                if (kTunedSynth4[0] && g_drv.moduleGetFunction(&t.synth4, mod, kTunedSynth4) != CUDA_SUCCESS) t.synth4 = nullptr;
-                if (kTunedGrad8[0] && g_drv.moduleGetFunction(&t.grad8, mod, kTunedGrad8) != CUDA_SUCCESS) t.grad8 = nullptr;
-                st = 1;
-            }
-            cudaGetLastError();
-            t.state = st;
-        }
-    }
-    return t.state == 1 ? &t : nullptr;
-}
-
-int launch_tuned(CUfunction f, dim3 grid, unsigned threads, size_t smem, cudaStream_t st, void** params, const char* what) {
-    if (smem > 48 * 1024) {
-        const CUresult r = g_drv.funcSetAttribute(f, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, (int)smem);
-        DDSP_REQUIRE(r == CUDA_SUCCESS, "%s: cannot reserve %zu B of shared memory (driver error %d)", what, smem, (int)r);
-    }
-    const CUresult r = g_drv.launchKernel(f, grid.x, grid.y, grid.z, threads, 1, 1, (unsigned)smem, st, params, nullptr);
-    ::ddsp::count_launch();
-    DDSP_REQUIRE(r == CUDA_SUCCESS, "%s: launch failed (driver error %d)", what, (int)r);
-    return 0;
-}
+TunedImage g_osc_image = {kTunedCubin, "DDSP_B200_TUNED_CUBIN"};
+TunedKernel g_tuned_synth4 = {kTunedSynth4}, g_tuned_grad8 = {kTunedGrad8};
 }  // namespace
 #endif
 
-extern "C" int ddsp_osc_tuned_sass(int mode) {
+namespace ddsp {
+int osc_tuned_mask() {
 #ifdef DDSP_HAVE_TUNED
-    if (mode == 0 || mode == 1) g_tuned_enabled.store(mode, std::memory_order_relaxed);
-    TunedDevice* t = tuned_kernels();
-    return t ? (t->synth4 ? 1 : 0) | (t->grad8 ? 2 : 0) : 0;
+    return (tuned_function(g_osc_image, g_tuned_synth4) ? 1 : 0) | (tuned_function(g_osc_image, g_tuned_grad8) ? 2 : 0);
 #else
-    (void)mode;
     return 0;
 #endif
 }
+}  // namespace ddsp
 
 extern "C" size_t ddsp_osc_state_bytes(int B, int T, int K) {
     if (B < 1 || T < 1 || K < 1) return 0;
@@ -844,10 +767,10 @@ extern "C" int ddsp_osc_synthesize(const float* f0, const float* a, const void* 
     }
 #ifdef DDSP_HAVE_TUNED
     if (R == 8) {
-        if (TunedDevice* t = tuned_kernels(); t && t->synth4) {
+        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_synth4)) {
             const float* cn_ = S.cn; const int* kact_ = S.kact; const SegFix* seg_ = S.seg;
             void* params[] = {&cn_, &a, &kact_, &seg_, &y, &z_save, &accumulate, &T, &K, &hop};
-            return launch_tuned(t->synth4, grid, (unsigned)((hop + 7) / 8), smem, st, params, "osc_synth_kernel (tuned)");
+            return tuned_launch(fn, grid, (unsigned)((hop + 7) / 8), smem, st, params, "osc_synth_kernel (tuned)");
         }
     }
 #endif
@@ -898,12 +821,12 @@ extern "C" int ddsp_osc_grad_segments(const float* g, const float* f0, const flo
     float2* gaseg = scratch_gaseg(scratch, B, T, K);
 #ifdef DDSP_HAVE_TUNED
     if (pick_R(hop, 16) == 16) {
-        if (TunedDevice* t = tuned_kernels(); t && t->grad8) {
+        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_grad8)) {
             const int NT = (hop + 15) / 16;
             const size_t smem = sizeof(float) * GRAD_CH * (((2 * NT + 3) & ~3) + 4);
             const int* kact_ = S.kact; const SegFix* seg_ = S.seg;
             void* params[] = {&g, &a, &z_save, &kact_, &seg_, &gseg, &gaseg, &T, &K, &hop};
-            return launch_tuned(t->grad8, dim3(T + 1, B), (unsigned)NT, smem, st, params, "osc_grad_kernel (tuned)");
+            return tuned_launch(fn, dim3(T + 1, B), (unsigned)NT, smem, st, params, "osc_grad_kernel (tuned)");
         }
     }
 #endif

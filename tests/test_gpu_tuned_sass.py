@@ -48,7 +48,7 @@ def test_tuned_image_is_loaded():
                                           (1, 3, 17, 44100, 4096), (5, 4, 1, 48000, 512)])
 def test_bits_equal_the_stock_kernels(B, T, K, sr, hop):
     have, tuned, stock = _both(lambda: _step(B, T, K, sr, hop, seed=B * 1000 + T))
-    assert have == 3
+    assert have & 3 == 3
     for name, x, y in zip(("y", "gc", "ga"), tuned, stock):
         assert torch.equal(x, y), f"{name}: tuned and stock kernels differ (max |d| = {float((x - y).abs().max()):.3e})"
 
@@ -57,7 +57,7 @@ def test_bits_equal_under_load_and_over_repeats():
     # 256 voices x 4 s: ~100 000 single-warp CTAs, every SM busy with 12 of them; three rounds
     for seed in range(3):
         have, tuned, stock = _both(lambda: _step(256, 375, 256, 48000, 512, seed=seed))
-        assert have == 3
+        assert have & 3 == 3
         for x, y in zip(tuned, stock):
             assert torch.equal(x, y)
 
@@ -80,7 +80,7 @@ def test_tuned_kernels_inside_a_cuda_graph():
         y.backward(gup)
         return y.detach(), c.grad, a.grad
 
-    assert lib.ddsp_osc_tuned_sass(1) == 3
+    assert lib.ddsp_osc_tuned_sass(1) & 3 == 3
     step()                                              # loads the image outside capture
     torch.cuda.synchronize()
     graph = torch.cuda.CUDAGraph()
@@ -100,3 +100,4 @@ def test_tuned_kernels_inside_a_cuda_graph():
         lib.ddsp_osc_tuned_sass(1)
     for x, y in zip(replayed, stock):
         assert torch.equal(x, y)
+
