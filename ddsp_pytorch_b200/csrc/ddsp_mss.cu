@@ -592,6 +592,66 @@ __device__ __forceinline__ float mss_generic_value(const MssCombineScale& d, int
     return x;
 }
 
+// Four consecutive samples per thread when every scale took the fast path (n >= 32, so a group of four aligned samples lies in
+// one slice of one pair: one set of index arithmetic and float4 loads for the four).  Groups that can receive mass reflected
+// from the padded margins (within n_max/2 of either end) take the scalar route sample by sample.  Every sample's sum is formed
+// in the order of mss_combine_kernel, so the two kernels give the same bits.
+__global__ void __launch_bounds__(256) mss_combine4_kernel(MssCombineArgs a, const float* __restrict__ gloss, float* __restrict__ out,
+                                                           int Nsig, int accumulate, int margin) {
+    const int m0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x), b = blockIdx.y;
+    if (m0 >= Nsig) return;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (m0 > margin && m0 + 3 < Nsig - 2 - margin) {
+        for (int s = 0; s < a.ns; ++s) {
+            const MssCombineScale& d = a.s[s];
+            const long long u = (long long)m0 + (d.n >> 1);
+            float4 x = *reinterpret_cast<const float4*>(d.gs + (size_t)b * d.U + u);
+            const int p = (int)(u >> d.lh), r = (int)u & ((1 << d.lh) - 1), j = r >> d.lt8, t = r & (d.T8 - 1), g = p & (d.G - 1);
+            if (!(g >= 2 || p == 0)) {
+                const size_t item_floats = (size_t)d.SL * 6 * d.T8;
+                const float* voice_side = d.side + (size_t)b * d.items_per_voice * item_floats;
+                auto side_of = [&](int q) {
+                    const int item = q >> d.lg, slot = d.G >= 2 ? (q & (d.G - 1)) - (d.G - 2) : 0;
+                    return voice_side + (size_t)item * item_floats + (size_t)slot * (6 * d.T8);
+                };
+                if (g == 0) {
+                    const float4 y = *reinterpret_cast<const float4*>(side_of(p - 1) + (j << d.lt8) + t);
+                    x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+                }
+                if (j < 2 && p >= 2) {
+                    const float4 y = *reinterpret_cast<const float4*>(side_of(p - 2) + ((j + 4) << d.lt8) + t);
+                    x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+                }
+            }
+            acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+        }
+    } else {
+        float av[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int e = 0; e < 4; ++e) {
+            const int m = m0 + e;
+            if (m >= Nsig) break;
+            const long long back = 2LL * (Nsig - 1) - m;
+            for (int s = 0; s < a.ns; ++s) {
+                const MssCombineScale& d = a.s[s];
+                const int half = d.n >> 1;
+                float v = mss_fast_value(d, b, (long long)m + half);
+                if (m >= 1 && m <= half) v += mss_fast_value(d, b, (long long)half - m);
+                if (m <= Nsig - 2 && back + half < d.U) v += mss_fast_value(d, b, back + half);
+                av[e] += v;
+            }
+        }
+        acc = make_float4(av[0], av[1], av[2], av[3]);
+    }
+    const float gl = gloss[0];
+    float4 r = make_float4(acc.x * gl, acc.y * gl, acc.z * gl, acc.w * gl);
+    float4* o = reinterpret_cast<float4*>(out + (size_t)b * Nsig + m0);
+    if (accumulate) {
+        const float4 q = *o;
+        r.x += q.x; r.y += q.y; r.z += q.z; r.w += q.w;
+    }
+    *o = r;
+}
+
 __global__ void __launch_bounds__(256) mss_combine_kernel(MssCombineArgs a, const float* __restrict__ gloss, float* __restrict__ out,
                                                           int Nsig, int accumulate) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
@@ -714,6 +774,17 @@ extern "C" int ddsp_mss_backward(const float* gloss, const void* scratch, float*
         d.items_per_voice = p.items_per_voice; d.U = p.U;
         auto lg2 = [](int v) { int k = 0; while ((1 << k) < v) ++k; return k; };
         d.lh = lg2(p.n / 2); d.lt8 = lg2(d.T8); d.lg = lg2(d.G);
+    }
+    bool vec4 = N % 4 == 0 && (reinterpret_cast<uintptr_t>(gx_out) & 15) == 0;
+    int margin = 0;
+    for (int s = 0; s < n_scales; ++s) {
+        vec4 = vec4 && ca.s[s].fast && ca.s[s].T8 >= 4 && ca.s[s].U % 4 == 0;
+        margin = ca.s[s].n / 2 > margin ? ca.s[s].n / 2 : margin;
+    }
+    if (vec4) {
+        mss_combine4_kernel<<<dim3((unsigned)((N / 4 + 255) / 256), (unsigned)B), 256, 0, static_cast<cudaStream_t>(stream)>>>(ca, gloss, gx_out, N, 0, margin);
+        DDSP_CHECK_LAUNCH("mss_combine4_kernel");
+        return 0;
     }
     mss_combine_kernel<<<dim3((unsigned)((N + 255) / 256), (unsigned)B), 256, 0, static_cast<cudaStream_t>(stream)>>>(ca, gloss, gx_out, N, 0);
     DDSP_CHECK_LAUNCH("mss_combine_kernel");
