@@ -497,7 +497,7 @@ def run_b200(args):
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args, sh), "clocks": clocks, "e2e": e2e,
             "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
-            # bit 0 / 1: synthesis / gradient kernel run from the hand-scheduled image (ddsp_pytorch_b200/sass_sched.py)
+            # bits 0 / 1 / 2: synthesis / gradient / pitch-gradient kernel run from the hand-scheduled image (sass_sched.py)
             "tuned_sass": int(lib.ddsp_osc_tuned_sass(-1)),
             "roofline": roofline, "roofline_fused": fused, "cpu_baseline": cpu, "kernels_ms": kernels_ms,
             "fp32_fma_peak_tflops_measured": fp32_peak, "fp32_fma_peak_tflops_nominal": fp32_nominal, "sharding": sharding,

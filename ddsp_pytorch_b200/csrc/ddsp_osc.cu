@@ -707,14 +707,15 @@ using namespace ddsp;
 #include "ddsp_osc_tuned.inc"      // kTunedCubin[], kTunedSynth4[], kTunedGrad8[] (mangled names, "" when not tuned)
 namespace {
 TunedImage g_osc_image = {kTunedCubin, "DDSP_B200_TUNED_CUBIN"};
-TunedKernel g_tuned_synth4 = {kTunedSynth4}, g_tuned_grad8 = {kTunedGrad8};
+TunedKernel g_tuned_synth4 = {kTunedSynth4}, g_tuned_grad8 = {kTunedGrad8}, g_tuned_dphase4 = {kTunedDphase4};
 }  // namespace
 #endif
 
 namespace ddsp {
 int osc_tuned_mask() {
 #ifdef DDSP_HAVE_TUNED
-    return (tuned_function(g_osc_image, g_tuned_synth4) ? 1 : 0) | (tuned_function(g_osc_image, g_tuned_grad8) ? 2 : 0);
+    return (tuned_function(g_osc_image, g_tuned_synth4) ? 1 : 0) | (tuned_function(g_osc_image, g_tuned_grad8) ? 2 : 0) |
+           (tuned_function(g_osc_image, g_tuned_dphase4) ? 4 : 0);
 #else
     return 0;
 #endif
@@ -936,14 +937,25 @@ extern "C" int ddsp_osc_backward_f0(const float* g, const float* f0, const float
         }                                                                                                               \
         osc_dphase_kernel<RP><<<grid, (hop + 2 * RP - 1) / (2 * RP), smem, st>>>(S.cn, a, S.kact, S.seg, g, q, T, K, hop); \
     } while (0)
-    switch (R) {
+    bool launched = false;
+#ifdef DDSP_HAVE_TUNED
+    if (R == 8) {
+        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_dphase4)) {
+            const float* cn_ = S.cn; const int* kact_ = S.kact; const SegFix* seg_ = S.seg;
+            void* params[] = {&cn_, &a, &kact_, &seg_, &g, &q, &T, &K, &hop};
+            if (tuned_launch(fn, grid, (unsigned)((hop + 7) / 8), smem, st, params, "osc_dphase_kernel (tuned)")) return 1;
+            launched = true;
+        }
+    }
+#endif
+    if (!launched) switch (R) {
         case 16: LAUNCH_DPH(8); break;
         case 8: LAUNCH_DPH(4); break;
         case 4: LAUNCH_DPH(2); break;
         default: LAUNCH_DPH(1); break;
     }
 #undef LAUNCH_DPH
-    DDSP_CHECK_LAUNCH("osc_dphase_kernel");
+    if (!launched) DDSP_CHECK_LAUNCH("osc_dphase_kernel");
     const long long N = (long long)T * hop;
     osc_revscan_kernel<<<B, 256, 0, st>>>(q, N, 6.283185307179586476925 / (double)sample_rate);
     DDSP_CHECK_LAUNCH("osc_revscan_kernel");

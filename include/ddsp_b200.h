@@ -103,7 +103,8 @@ int ddsp_osc_forward_noalloc(const float* f0, const float* c, const float* a, fl
  * instructions in an order that feeds the FMA pipe from the operand reuse cache (ddsp_pytorch_b200/sass_sched.py; results are
  * bit-identical).  The image is loaded through the driver API on the first oscillator call of a device -- make that call
  * outside stream capture -- and used from then on.  mode 1 / 0 switches it on (default) / off for the calling process,
- * any other value only queries; returns bit 0 = synthesis, bit 1 = gradient kernel tuned and in use on the current device. */
+ * any other value only queries; returns bit 0 = synthesis, bit 1 = gradient, bit 2 = d/d f0 synthesis-pass kernel tuned and in
+ * use on the current device. */
 int ddsp_osc_tuned_sass(int mode);
 
 /* OscillatorBank.live, harmonic_oscillator.py:64-75: as forward, but voice 0 starts harmonic k from the

@@ -26,20 +26,21 @@ def _step(B, T, K, sr, hop, seed):
     from ddsp_pytorch_b200.synthetic import synthetic_f0
     g = torch.Generator(device="cuda").manual_seed(seed)
     f0 = synthetic_f0(B, T, sr, hop, seed)[..., 0].cuda() if sr >= 44100 else 80.0 + 600.0 * torch.rand(B, T, device="cuda", generator=g)
+    f0 = f0.clone().requires_grad_(True)               # the pitch gradient runs a third hand-scheduled kernel
     c = torch.rand(B, T, K, device="cuda", generator=g).requires_grad_(True)
     a = torch.rand(B, T, device="cuda", generator=g).requires_grad_(True)
     gup = torch.randn(B, T * hop, device="cuda", generator=g)
     y = ops.oscillator_bank(f0, c, a, sr, hop)
     (y * gup).sum().backward()
     torch.cuda.synchronize()
-    return y.detach().clone(), c.grad.clone(), a.grad.clone()
+    return y.detach().clone(), c.grad.clone(), a.grad.clone(), f0.grad.clone()
 
 
 def test_tuned_image_is_loaded():
     from ddsp_pytorch_b200 import _lib
     lib = _lib.load()
     torch.zeros(1, device="cuda")
-    assert lib.ddsp_osc_tuned_sass(1) == 3, "the library was built without the hand-scheduled kernels, or the driver refused them"
+    assert lib.ddsp_osc_tuned_sass(1) == 7, "the library was built without the hand-scheduled kernels, or the driver refused them"
 
 
 @pytest.mark.parametrize("B,T,K,sr,hop", [(2, 375, 256, 48000, 512), (16, 125, 100, 16000, 512), (3, 20, 100, 16000, 512),
@@ -49,7 +50,7 @@ def test_tuned_image_is_loaded():
 def test_bits_equal_the_stock_kernels(B, T, K, sr, hop):
     have, tuned, stock = _both(lambda: _step(B, T, K, sr, hop, seed=B * 1000 + T))
     assert have & 3 == 3
-    for name, x, y in zip(("y", "gc", "ga"), tuned, stock):
+    for name, x, y in zip(("y", "gc", "ga", "gf0"), tuned, stock):
         assert torch.equal(x, y), f"{name}: tuned and stock kernels differ (max |d| = {float((x - y).abs().max()):.3e})"
 
 
