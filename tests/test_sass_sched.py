@@ -139,17 +139,17 @@ def test_tuned_loops_respect_latencies_and_waits(images):
         for x in b:
             key = (x["lo"], x["hi"] & CTL_MASK)
             assert x["ctl"]["wait"] & want[key] == want[key], name
-        # a scoreboard index is armed a cycle or two after its instruction issues: nothing that waits on it issues right behind
-        t2 = 0
-        armed = {}
-        for ins in b:
-            for bit in range(6):
-                if (ins["ctl"]["wait"] >> bit) & 1 and bit in armed:
-                    assert t2 - armed[bit] >= 2, f"{name}: {ins['text']} waits on index {bit} {t2 - armed[bit]} cycle(s) after it was armed"
-            for idx in (ins["ctl"]["wb"], ins["ctl"]["rb"]):
-                if idx != 7:
-                    armed[idx] = t2
-            t2 += ins["ctl"]["stall"]
+        # a scoreboard index is armed a cycle or two after its instruction issues: an instruction that needs the result (or
+        # overwrites the destination) does not issue right behind it
+        for k, prod in enumerate(b):
+            if prod["ctl"]["wb"] == 7:
+                continue
+            for q in range(k + 1, len(b)):
+                if b[q]["defs"] & prod["defs"] or b[q]["uses"] & prod["defs"]:
+                    assert when[q] - when[k] >= 2, f"{name}: {b[q]['text']} issues {when[q] - when[k]} cycle(s) after {prod['text']}"
+                    assert (b[q]["ctl"]["wait"] >> prod["ctl"]["wb"]) & 1
+                if b[q]["defs"] & prod["defs"]:
+                    break
         # a store's sources may only be overwritten by an instruction that waits for the store's read barrier
         for i, st in enumerate(b):
             if st["base"] == "STS" and st["ctl"]["rb"] != 7:
