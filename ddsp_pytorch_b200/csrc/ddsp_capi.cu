@@ -72,11 +72,18 @@ bool driver_ready() {
 void tuned_enable(int on) { g_tuned_on.store(on ? 1 : 0, std::memory_order_relaxed); }
 int tuned_enabled() { return g_tuned_on.load(std::memory_order_relaxed); }
 
-CUfunction tuned_function(TunedImage& img, TunedKernel& k) {
+CUfunction tuned_function(TunedImage& img, TunedKernel& k, cudaStream_t st, bool have_stream) {
     if (!tuned_enabled() || !k.name || !k.name[0]) return nullptr;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= TUNED_MAX_DEVICES) return nullptr;
     if (k.state[dev] == 0 || img.state[dev] == 0) {
+        if (have_stream) {
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
+                cudaGetLastError();
+                return nullptr;
+            }
+        }
         std::lock_guard<std::mutex> lock(img.lock);
         if (img.state[dev] == 0) {
             int st = -1;

@@ -768,7 +768,7 @@ extern "C" int ddsp_osc_synthesize(const float* f0, const float* a, const void* 
     }
 #ifdef DDSP_HAVE_TUNED
     if (R == 8) {
-        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_synth4)) {
+        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_synth4, st, true)) {
             const float* cn_ = S.cn; const int* kact_ = S.kact; const SegFix* seg_ = S.seg;
             void* params[] = {&cn_, &a, &kact_, &seg_, &y, &z_save, &accumulate, &T, &K, &hop};
             return tuned_launch(fn, grid, (unsigned)((hop + 7) / 8), smem, st, params, "osc_synth_kernel (tuned)");
@@ -822,7 +822,7 @@ extern "C" int ddsp_osc_grad_segments(const float* g, const float* f0, const flo
     float2* gaseg = scratch_gaseg(scratch, B, T, K);
 #ifdef DDSP_HAVE_TUNED
     if (pick_R(hop, 16) == 16) {
-        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_grad8)) {
+        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_grad8, st, true)) {
             const int NT = (hop + 15) / 16;
             const size_t smem = sizeof(float) * GRAD_CH * (((2 * NT + 3) & ~3) + 4);
             const int* kact_ = S.kact; const SegFix* seg_ = S.seg;
@@ -940,7 +940,7 @@ extern "C" int ddsp_osc_backward_f0(const float* g, const float* f0, const float
     bool launched = false;
 #ifdef DDSP_HAVE_TUNED
     if (R == 8) {
-        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_dphase4)) {
+        if (CUfunction fn = tuned_function(g_osc_image, g_tuned_dphase4, st, true)) {
             const float* cn_ = S.cn; const int* kact_ = S.kact; const SegFix* seg_ = S.seg;
             void* params[] = {&cn_, &a, &kact_, &seg_, &g, &q, &T, &K, &hop};
             if (tuned_launch(fn, grid, (unsigned)((hop + 7) / 8), smem, st, params, "osc_dphase_kernel (tuned)")) return 1;

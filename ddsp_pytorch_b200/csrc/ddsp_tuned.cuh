@@ -30,8 +30,10 @@ struct TunedKernel {
     CUfunction fn[TUNED_MAX_DEVICES];
 };
 
-// the kernel's function in the image on the current device, or nullptr (then launch the compiled-in kernel)
-CUfunction tuned_function(TunedImage& img, TunedKernel& k);
+// the kernel's function in the image on the current device, or nullptr (then launch the compiled-in kernel).  `st` is the
+// stream the launch will go to: while it is capturing, an image that is not loaded yet stays unloaded (loading is not a
+// capturable operation) and the compiled-in kernel is captured instead.
+CUfunction tuned_function(TunedImage& img, TunedKernel& k, cudaStream_t st = nullptr, bool have_stream = false);
 int tuned_launch(CUfunction f, dim3 grid, unsigned threads, size_t smem, cudaStream_t st, void** params, const char* what);
 void tuned_enable(int on);
 int tuned_enabled();

@@ -102,3 +102,31 @@ def test_tuned_kernels_inside_a_cuda_graph():
     for x, y in zip(replayed, stock):
         assert torch.equal(x, y)
 
+
+
+def test_first_oscillator_call_inside_capture():
+    """loading the image is not capturable: a process whose FIRST oscillator call is being captured gets the compiled-in
+    kernels in that graph (and a valid graph); the image is loaded by the next eager call"""
+    import os
+    import subprocess
+    import sys
+    code = """
+import torch
+from ddsp_pytorch_b200 import _lib, ops
+lib = _lib.load()
+f0 = 200.0 + torch.zeros(2, 20, device="cuda"); c = torch.rand(2, 20, 64, device="cuda"); a = torch.rand(2, 20, device="cuda")
+g = torch.cuda.CUDAGraph(); s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
+with torch.cuda.stream(s):
+    with torch.cuda.graph(g, stream=s):
+        y = ops.oscillator_bank(f0, c, a, 16000, 512)
+g.replay(); torch.cuda.synchronize()
+y_graph = y.clone()
+y_eager = ops.oscillator_bank(f0, c, a, 16000, 512)
+torch.cuda.synchronize()
+assert lib.ddsp_osc_tuned_sass(-1) & 1 == 1
+assert torch.equal(y_graph, y_eager)
+print("ok")
+"""
+    root = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-500:] + r.stderr[-1500:]
