@@ -259,11 +259,30 @@ def bench_ctrl(args, dev):
 
         R, J = B * T, K + 1 + NB
         res = {"workload": f"controller tail R={R} U={U} J={J}", "flop_fwd": 2.0 * R * U * J}
-        for name, fn in (("fused", fused), ("torch", stock)):
+        # "fused" = what ops.controller_heads picks for this R (tcgen05 from ops.CTRL_TC_MIN_ROWS rows); "ffma" = the CUDA-core
+        # product forced; each as eager calls (host launch time included) and as a CUDA-graph replay (device time)
+        auto_rows = ops.CTRL_TC_MIN_ROWS
+        res["fused_path"] = "tcgen05" if ops._ctrl_use_tensor_cores(R, U) else "ffma"
+        for name, fn, rows in (("fused", fused, auto_rows), ("ffma", fused, 0), ("torch", stock, auto_rows)):
+            ops.CTRL_TC_MIN_ROWS = rows
             with torch.no_grad():
                 res[f"{name}_fwd_ms"] = ev_time(lambda: fn(False), args.reps)
             res[f"{name}_fwd_bwd_ms"] = ev_time(lambda: fn(True), args.reps)
-        res["fused_fwd_TFLOPs"] = res["flop_fwd"] / (res["fused_fwd_ms"] * 1e-3) / 1e12
+            if name != "torch":
+                for bwd, key in ((False, "fwd"), (True, "fwd_bwd")):
+                    x.grad = None
+                    for t in ps:
+                        t.grad = None
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        if bwd:
+                            fn(True)
+                        else:
+                            with torch.no_grad():
+                                fn(False)
+                    res[f"{name}_{key}_graph_ms"] = ev_time(graph.replay, args.reps)
+        ops.CTRL_TC_MIN_ROWS = auto_rows
+        res["fused_fwd_TFLOPs"] = res["flop_fwd"] / (res["fused_fwd_graph_ms"] * 1e-3) / 1e12
         out.append(res)
     return out
 

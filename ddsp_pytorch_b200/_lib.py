@@ -54,6 +54,9 @@ SIGNATURES = {
     "ddsp_ctrl_heads_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "ddsp_ctrl_heads_forward": (_i, [_p] * 11 + [_i, _i, _i, _i, _p]),
     "ddsp_ctrl_heads_backward": (_i, [_p] * 16 + [_i, _i, _i, _i, _p]),
+    "ddsp_ctrl_heads_tc_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "ddsp_ctrl_heads_forward_tc": (_i, [_p] * 12 + [_i, _i, _i, _i, _p]),
+    "ddsp_ctrl_heads_backward_tc": (_i, [_p] * 16 + [_i, _i, _i, _i, _p]),
     "ddsp_loudness_frames": (_i, [_i, _i, _i]),
     "ddsp_loudness_forward": (_i, [_p, _p, _p, _i, _i, _i, _i, _p]),
     "ddsp_fft_c2c": (_i, [_p, _p, _i, C.c_longlong, _i, _i, _p]),

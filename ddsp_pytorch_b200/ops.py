@@ -492,6 +492,15 @@ def loudness(signal: torch.Tensor, a_weight: torch.Tensor, n_fft: int, hop: int)
     return out
 
 
+# Rows from which the Controller tail runs on the tensor cores (csrc/ddsp_ctrl.cu: tcgen05 path); below it the split
+# pre-passes' launches cost more than the product.  0 disables the path (tests set it either way).
+CTRL_TC_MIN_ROWS = 256
+
+
+def _ctrl_use_tensor_cores(R: int, U: int) -> bool:
+    return CTRL_TC_MIN_ROWS > 0 and R >= CTRL_TC_MIN_ROWS and U >= 64 and U % 8 == 0
+
+
 class _ControllerHeads(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w_c, b_c, w_a, b_a, w_h, b_h):
@@ -512,11 +521,18 @@ class _ControllerHeads(torch.autograd.Function):
             a = torch.empty(*lead, 1, dtype=torch.float32, device=dev)
             H = torch.empty(*lead, NB, dtype=torch.float32, device=dev)
             z = torch.empty(R, lib.ddsp_ctrl_heads_ldz(K, NB), dtype=torch.float32, device=dev) if need_grad else None
-            _lib.call("ddsp_ctrl_heads_forward", x_.data_ptr(), *(p.data_ptr() for p in params), c.data_ptr(), a.data_ptr(),
-                      H.data_ptr(), z.data_ptr() if z is not None else None, R, U, K, NB, _stream())
+            tc = _ctrl_use_tensor_cores(R, U)
+            if tc:
+                ws = _bytes(lib.ddsp_ctrl_heads_tc_workspace_bytes(R, U, K, NB, 0), dev)
+                _lib.call("ddsp_ctrl_heads_forward_tc", x_.data_ptr(), *(p.data_ptr() for p in params), c.data_ptr(), a.data_ptr(),
+                          H.data_ptr(), z.data_ptr() if z is not None else None, ws.data_ptr(), R, U, K, NB, _stream())
+            else:
+                _lib.call("ddsp_ctrl_heads_forward", x_.data_ptr(), *(p.data_ptr() for p in params), c.data_ptr(), a.data_ptr(),
+                          H.data_ptr(), z.data_ptr() if z is not None else None, R, U, K, NB, _stream())
         if need_grad:
             ctx.save_for_backward(x_, params[0], params[2], params[4], z)
             ctx.dims = (R, U, K, NB)
+            ctx.tc = tc
             ctx.meta = (x.shape, x.dtype, x.requires_grad, [p.dtype for p in (w_c, b_c, w_a, b_a, w_h, b_h)])
         return c, a, H
 
@@ -532,8 +548,9 @@ class _ControllerHeads(torch.autograd.Function):
             mk = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)  # noqa: E731
             gx = mk(R, U) if x_req else None
             outs = [mk(K, U), mk(K), mk(1, U), mk(1), mk(NB, U), mk(NB)]
-            ws = _bytes(lib.ddsp_ctrl_heads_workspace_bytes(R, U, K, NB), dev)
-            _lib.call("ddsp_ctrl_heads_backward", x_.data_ptr(), w_c.data_ptr(), w_a.data_ptr(), w_h.data_ptr(), z.data_ptr(),
+            ws = _bytes(lib.ddsp_ctrl_heads_tc_workspace_bytes(R, U, K, NB, 1) if ctx.tc else
+                        lib.ddsp_ctrl_heads_workspace_bytes(R, U, K, NB), dev)
+            _lib.call("ddsp_ctrl_heads_backward_tc" if ctx.tc else "ddsp_ctrl_heads_backward", x_.data_ptr(), w_c.data_ptr(), w_a.data_ptr(), w_h.data_ptr(), z.data_ptr(),
                       *(None if g is None else g.data_ptr() for g in gs), None if gx is None else gx.data_ptr(),
                       *(o.data_ptr() for o in outs), ws.data_ptr(), R, U, K, NB, _stream())
         gx = None if gx is None else gx.view(x_shape).to(x_dtype)

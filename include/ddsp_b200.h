@@ -274,6 +274,21 @@ int ddsp_ctrl_heads_backward(const float* x, const float* w_c, const float* w_a,
                              const float* z, const float* g_c, const float* g_a, const float* g_h,
                              float* gx, float* gw_c, float* gb_c, float* gw_a, float* gb_a, float* gw_h,
                              float* gb_h, void* workspace, int R, int U, int K, int NB, void* stream);
+/* The same two calls on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands by TMA): both
+ * operands as bf16 x 3 splits, six products in fp32 -- an fp32-accurate product, deterministic.  For R of a few hundred
+ * rows and more (below that the launches of the split pre-passes cost more than the product); U % 8 == 0.
+ *   workspace: ddsp_ctrl_heads_tc_workspace_bytes(R,U,K,NB, backward != 0) bytes, 16-byte aligned (0: bad arguments).
+ *   z as above; the tensor-core backward takes the z either forward wrote. */
+size_t ddsp_ctrl_heads_tc_workspace_bytes(int R, int U, int K, int NB, int backward);
+int ddsp_ctrl_heads_forward_tc(const float* x, const float* w_c, const float* b_c, const float* w_a,
+                               const float* b_a, const float* w_h, const float* b_h, float* c, float* a,
+                               float* H, float* z, void* workspace, int R, int U, int K, int NB,
+                               void* stream);
+int ddsp_ctrl_heads_backward_tc(const float* x, const float* w_c, const float* w_a, const float* w_h,
+                                const float* z, const float* g_c, const float* g_a, const float* g_h,
+                                float* gx, float* gw_c, float* gb_c, float* gw_a, float* gb_a,
+                                float* gw_h, float* gb_h, void* workspace, int R, int U, int K, int NB,
+                                void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * The transform underneath the reverb and the spectral loss, on its own: `batch` complex FFTs of

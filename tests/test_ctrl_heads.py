@@ -70,8 +70,16 @@ def test_kernel_matches_reference_fixture():
                                        (16, 250, 512, 100, 65),     # config/default.py: J = 166, ld 168
                                        (1, 1, 512, 180, 195),       # rt/synth.py: one frame
                                        (2, 37, 24, 3, 2),           # ragged everything
-                                       (1, 300, 128, 256, 65)])
-def test_kernel_matches_fp64_torch(B, T, U, K, NB):
+                                       (1, 300, 128, 256, 65),
+                                       (4, 100, 64, 3, 2),          # J = 6: far fewer output columns than a tile
+                                       (3, 130, 72, 50, 20)])       # U not a multiple of the 64-wide K panel
+@pytest.mark.parametrize("path", ["ffma", "tcgen05", "auto"])
+def test_kernel_matches_fp64_torch(B, T, U, K, NB, path, monkeypatch):
+    from ddsp_pytorch_b200 import ops
+    # "tcgen05": every shape the tensor-core path accepts (U >= 64, U % 8 == 0) goes through it, down to one row
+    monkeypatch.setattr(ops, "CTRL_TC_MIN_ROWS", {"ffma": 0, "tcgen05": 1, "auto": ops.CTRL_TC_MIN_ROWS}[path])
+    if path == "tcgen05":
+        assert ops._ctrl_use_tensor_cores(B * T, U) == (U >= 64 and U % 8 == 0)
     torch.manual_seed(B * 1000 + T)
     dev = "cuda"
     x = torch.randn(B, T, U, device=dev)
