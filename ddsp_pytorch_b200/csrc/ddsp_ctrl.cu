@@ -51,6 +51,14 @@ __device__ __forceinline__ float msig_grad_fast(float z) {
     return 2.0f * MSIG_P * __expf(-MSIG_P * (fmaxf(-z, 0.f) + __logf(d))) * one_minus;
 }
 
+__device__ __forceinline__ void split3(float v, __nv_bfloat16 (&h)[3]) {
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        h[s] = __float2bfloat16_rn(v);
+        v -= __bfloat162float(h[s]);                        // exact: the remainder fits fp32
+    }
+}
+
 enum { EPI_HEADS = 0, EPI_STORE = 1 };
 
 struct HeadsOut {
@@ -202,7 +210,8 @@ constexpr int DZ_ROWS = 32, DZ_TX = 128, DZ_TY = 4;
 template <bool FAST>
 __global__ void __launch_bounds__(DZ_TX * DZ_TY)
 ctrl_dz_kernel(const float* __restrict__ z, const float* __restrict__ gc, const float* __restrict__ ga,
-               const float* __restrict__ gH, float* __restrict__ dz, float* __restrict__ bpart, int R, int K, int NB, int ldz) {
+               const float* __restrict__ gH, float* __restrict__ dz, float* __restrict__ bpart, int R, int K, int NB, int ldz,
+               __nv_bfloat16* __restrict__ planes, int ld_planes, size_t plane) {
     __shared__ float red[DZ_TY][DZ_TX];
     const int J = K + 1 + NB;
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -220,6 +229,12 @@ ctrl_dz_kernel(const float* __restrict__ z, const float* __restrict__ gc, const 
                 const float zz = z[(size_t)r * ldz + j];
                 const float d = g * (FAST ? msig_grad_fast(zz) : msig_grad(zz));
                 dz[(size_t)r * ldz + j] = d;
+                if (planes) {                          // the bf16 x 3 split the tensor-core product of gx reads (K-major in j)
+                    __nv_bfloat16 h[3];
+                    split3(d, h);
+#pragma unroll
+                    for (int s = 0; s < 3; ++s) planes[s * plane + (size_t)r * ld_planes + j] = h[s];
+                }
                 sum += d;
             }
         } else if (j < ldz) {
@@ -439,45 +454,50 @@ ctrl_tc_gemm_kernel(const __grid_constant__ ctc::Maps maps, int M, int N, int Kd
     }
 }
 
-__device__ __forceinline__ void split3(float v, __nv_bfloat16 (&h)[3]) {
-#pragma unroll
-    for (int s = 0; s < 3; ++s) {
-        h[s] = __float2bfloat16_rn(v);
-        v -= __bfloat162float(h[s]);                        // exact: the remainder fits fp32
-    }
-}
+// One launch splits up to three matrices (fewer launches matter: the path is host-bound in eager mode at the shapes it serves).
+struct SplitJob {
+    Rows3 src;
+    int rows, cols, ld_out;
+    __nv_bfloat16* planes;
+    size_t plane;
+    unsigned gx, gy;              // this job's grid
+};
+struct SplitJobs { SplitJob job[3]; };
 
 // planes[s][r][c] (pitch ld_out) = split s of src(r, c); four columns per thread (cols % 4 == 0, rows 16-byte aligned)
-__global__ void __launch_bounds__(256) ctrl_split_rows_kernel(Rows3 src, int rows, int cols, __nv_bfloat16* __restrict__ planes, int ld_out,
-                                                              size_t plane) {
-    const int c4 = cols >> 2;
-    const size_t total = (size_t)rows * c4;
-    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+__global__ void __launch_bounds__(256) ctrl_split_rows_kernel(const __grid_constant__ SplitJobs jobs) {
+    const SplitJob& jb = jobs.job[blockIdx.y];
+    if (blockIdx.x >= jb.gx) return;
+    const int c4 = jb.cols >> 2;
+    const size_t total = (size_t)jb.rows * c4;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)jb.gx * blockDim.x) {
         const int r = (int)(e / c4), c = (int)(e % c4) * 4;
-        const float4 v = *reinterpret_cast<const float4*>(src.row(r) + c);
+        const float4 v = *reinterpret_cast<const float4*>(jb.src.row(r) + c);
         __nv_bfloat16 h[4][3];
         split3(v.x, h[0]); split3(v.y, h[1]); split3(v.z, h[2]); split3(v.w, h[3]);
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
             __nv_bfloat162 lo, hi;
             lo.x = h[0][s]; lo.y = h[1][s]; hi.x = h[2][s]; hi.y = h[3][s];
-            __nv_bfloat162* dst = reinterpret_cast<__nv_bfloat162*>(planes + s * plane + (size_t)r * ld_out + c);
+            __nv_bfloat162* dst = reinterpret_cast<__nv_bfloat162*>(jb.planes + s * jb.plane + (size_t)r * jb.ld_out + c);
             dst[0] = lo;
             dst[1] = hi;
         }
     }
 }
 
-// planes[s][c][r] (pitch ld_out) = split s of src(r, c): 32 x 64 tiles through shared memory, two rows per store
-__global__ void __launch_bounds__(256) ctrl_split_transpose_kernel(Rows3 src, int rows, int cols, __nv_bfloat16* __restrict__ planes, int ld_out,
-                                                                   size_t plane) {
+// planes[s][c][r] (pitch ld_out) = split s of src(r, c): 64 x 32 tiles through shared memory, two rows per store
+__global__ void __launch_bounds__(256) ctrl_split_transpose_kernel(const __grid_constant__ SplitJobs jobs) {
     __shared__ float tile[64][33];
+    const SplitJob& jb = jobs.job[blockIdx.z];
+    if (blockIdx.x >= jb.gx || blockIdx.y >= jb.gy) return;
+    const int rows = jb.rows, cols = jb.cols;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;              // 32 x 8
     const int r0 = blockIdx.x * 64, c0 = blockIdx.y * 32;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int r = r0 + ty + 8 * i, c = c0 + tx;
-        tile[ty + 8 * i][tx] = (r < rows && c < cols) ? src.row(r)[c] : 0.f;
+        tile[ty + 8 * i][tx] = (r < rows && c < cols) ? jb.src.row(r)[c] : 0.f;
     }
     __syncthreads();
 #pragma unroll
@@ -489,11 +509,36 @@ __global__ void __launch_bounds__(256) ctrl_split_transpose_kernel(Rows3 src, in
         split3(tile[2 * tx + 1][ty + 8 * i], h1);
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
-            __nv_bfloat16* dst = planes + s * plane + (size_t)c * ld_out + r;
+            __nv_bfloat16* dst = jb.planes + s * jb.plane + (size_t)c * jb.ld_out + r;
             if (r + 1 < rows) { __nv_bfloat162 p; p.x = h0[s]; p.y = h1[s]; *reinterpret_cast<__nv_bfloat162*>(dst) = p; }
             else dst[0] = h0[s];
         }
     }
+}
+
+static SplitJob split_rows_job(Rows3 src, int rows, int cols, __nv_bfloat16* planes, int ld_out) {
+    const size_t items = (size_t)rows * (cols / 4);
+    return SplitJob{src, rows, cols, ld_out, planes, (size_t)rows * ld_out, (unsigned)std::min<size_t>((items + 255) / 256, 148 * 16), 1};
+}
+static SplitJob split_transpose_job(Rows3 src, int rows, int cols, __nv_bfloat16* planes, int ld_out) {
+    return SplitJob{src, rows, cols, ld_out, planes, (size_t)cols * ld_out, (unsigned)((rows + 63) / 64), (unsigned)((cols + 31) / 32)};
+}
+static int launch_split_rows(const SplitJob* jb, int n, cudaStream_t st) {
+    SplitJobs jobs{};
+    unsigned gx = 1;
+    for (int i = 0; i < n; ++i) { jobs.job[i] = jb[i]; gx = std::max(gx, jb[i].gx); }
+    ctrl_split_rows_kernel<<<dim3(gx, n), 256, 0, st>>>(jobs);
+    DDSP_CHECK_LAUNCH("ctrl_split_rows_kernel");
+    return 0;
+}
+static int launch_split_transpose(const SplitJob* jb, int n, cudaStream_t st) {
+    SplitJobs jobs{};
+    unsigned gx = 1, gy = 1;
+    for (int i = 0; i < n; ++i) { jobs.job[i] = jb[i]; gx = std::max(gx, jb[i].gx); gy = std::max(gy, jb[i].gy); }
+    DDSP_REQUIRE(gy <= 65535, "ctrl_split_transpose_kernel: matrix too wide");
+    ctrl_split_transpose_kernel<<<dim3(gx, gy, n), 256, 0, st>>>(jobs);
+    DDSP_CHECK_LAUNCH("ctrl_split_transpose_kernel");
+    return 0;
 }
 
 struct CtrlTcPlan {
@@ -552,8 +597,6 @@ static int ctrl_tc_launch(const ctc::Maps& maps, int M, int N, int Kd, int kspli
     return 0;
 }
 
-static unsigned split_blocks(size_t work_items) { return (unsigned)std::min<size_t>((work_items + 255) / 256, 148 * 16); }
-
 }  // namespace ddsp
 
 using namespace ddsp;
@@ -603,7 +646,7 @@ extern "C" int ddsp_ctrl_heads_backward(const float* x, const float* w_c, const 
     float* part = static_cast<float*>(workspace);
     float* bpart = part + p.part_floats;
     float* dz = bpart + p.bpart_floats;                  // part_floats and bpart_floats are multiples of 4
-    ctrl_dz_kernel<false><<<p.tiles, dim3(DZ_TX, DZ_TY), 0, st>>>(z, g_c, g_a, g_h, dz, bpart, R, K, NB, p.ldz);
+    ctrl_dz_kernel<false><<<p.tiles, dim3(DZ_TX, DZ_TY), 0, st>>>(z, g_c, g_a, g_h, dz, bpart, R, K, NB, p.ldz, nullptr, 0, 0);
     DDSP_CHECK_LAUNCH("ctrl_dz_kernel");
     HeadsOut none{};
     if (gx) {       // gx[R,U] = dZ[R,J] * Wcat[J,U]
@@ -649,10 +692,10 @@ extern "C" int ddsp_ctrl_heads_forward_tc(const float* x, const float* w_c, cons
     __nv_bfloat16* xp = reinterpret_cast<__nv_bfloat16*>(ws + p.off_xp);
     __nv_bfloat16* wp = reinterpret_cast<__nv_bfloat16*>(ws + p.off_wp);
     Rows3 W{{w_c, w_a, w_h}, K, K + 1, U};
-    ctrl_split_rows_kernel<<<split_blocks((size_t)R * (U / 4)), 256, 0, st>>>(rows_plain(x, U), R, U, xp, U, (size_t)R * U);
-    DDSP_CHECK_LAUNCH("ctrl_split_rows_kernel<x>");
-    ctrl_split_rows_kernel<<<split_blocks((size_t)p.J * (U / 4)), 256, 0, st>>>(W, p.J, U, wp, U, (size_t)p.J * U);
-    DDSP_CHECK_LAUNCH("ctrl_split_rows_kernel<w>");
+    {
+        const SplitJob jb[2] = {split_rows_job(rows_plain(x, U), R, U, xp, U), split_rows_job(W, p.J, U, wp, U)};
+        if (int rc = launch_split_rows(jb, 2, st)) return rc;
+    }
     ctc::Maps maps;
     if (int rc = ctrl_tc_maps(maps, xp, (uint64_t)R, (uint64_t)U, wp, (uint64_t)p.J, (uint64_t)U, (uint64_t)U)) return rc;
     HeadsOut ho{{b_c, b_a, b_h}, c, a, H, z, K, NB, p.ldz};
@@ -680,25 +723,22 @@ extern "C" int ddsp_ctrl_heads_backward_tc(const float* x, const float* w_c, con
     __nv_bfloat16* wt = reinterpret_cast<__nv_bfloat16*>(ws + p.off_wt);
     __nv_bfloat16* dzt = reinterpret_cast<__nv_bfloat16*>(ws + p.off_dzt);
     __nv_bfloat16* xt = reinterpret_cast<__nv_bfloat16*>(ws + p.off_xt);
-    ctrl_dz_kernel<true><<<p.tiles, dim3(DZ_TX, DZ_TY), 0, st>>>(z, g_c, g_a, g_h, dz, bpart, R, K, NB, p.ldz);
+    ctrl_dz_kernel<true><<<p.tiles, dim3(DZ_TX, DZ_TY), 0, st>>>(z, g_c, g_a, g_h, dz, bpart, R, K, NB, p.ldz, gx ? dzp : nullptr, p.J8, (size_t)R * p.J8);
     DDSP_CHECK_LAUNCH("ctrl_dz_kernel");
     HeadsOut none{};
     ctc::Maps maps;
-    if (gx) {       // gx[R,U] = dZ[R,J] * Wcat[J,U]: A = dZ (K-major in J), B = Wcat^T [U,J]
+    {               // the transposed operands of both products in one launch: Wcat^T [U,J] (for gx), dZ^T [J,R] and X^T [U,R]
         Rows3 W{{w_c, w_a, w_h}, K, K + 1, U};
-        ctrl_split_rows_kernel<<<split_blocks((size_t)R * (p.ldz / 4)), 256, 0, st>>>(rows_plain(dz, p.ldz), R, p.ldz, dzp, p.J8, (size_t)R * p.J8);
-        DDSP_CHECK_LAUNCH("ctrl_split_rows_kernel<dz>");
-        ctrl_split_transpose_kernel<<<dim3((p.J + 63) / 64, (U + 31) / 32), 256, 0, st>>>(W, p.J, U, wt, p.J8, (size_t)U * p.J8);
-        DDSP_CHECK_LAUNCH("ctrl_split_transpose_kernel<w>");
+        const SplitJob jb[3] = {split_transpose_job(rows_plain(dz, p.ldz), R, p.J, dzt, p.R8), split_transpose_job(rows_plain(x, U), R, U, xt, p.R8),
+                                split_transpose_job(W, p.J, U, wt, p.J8)};
+        if (int rc = launch_split_transpose(jb, gx ? 3 : 2, st)) return rc;
+    }
+    if (gx) {       // gx[R,U] = dZ[R,J] * Wcat[J,U]: A = dZ (K-major in J, planes written by ctrl_dz_kernel), B = Wcat^T [U,J]
         if (int rc = ctrl_tc_maps(maps, dzp, (uint64_t)R, (uint64_t)p.J8, wt, (uint64_t)U, (uint64_t)p.J8, (uint64_t)p.J)) return rc;
         if (int rc = ctrl_tc_launch<EPI_STORE>(maps, R, U, p.J, (p.J + ctc::BK - 1) / ctc::BK * ctc::BK, 1, gx, U, none, st, "ctrl_tc_gemm_kernel<dx>"))
             return rc;
     }
     {               // partial[s][J,U] = dZ[rows of split s]^T * X[rows of split s]: A = dZ^T [J,R], B = X^T [U,R]
-        ctrl_split_transpose_kernel<<<dim3((R + 63) / 64, (p.J + 31) / 32), 256, 0, st>>>(rows_plain(dz, p.ldz), R, p.J, dzt, p.R8, (size_t)p.J * p.R8);
-        DDSP_CHECK_LAUNCH("ctrl_split_transpose_kernel<dz>");
-        ctrl_split_transpose_kernel<<<dim3((R + 63) / 64, (U + 31) / 32), 256, 0, st>>>(rows_plain(x, U), R, U, xt, p.R8, (size_t)U * p.R8);
-        DDSP_CHECK_LAUNCH("ctrl_split_transpose_kernel<x>");
         if (int rc = ctrl_tc_maps(maps, dzt, (uint64_t)p.J, (uint64_t)p.R8, xt, (uint64_t)U, (uint64_t)p.R8, (uint64_t)R)) return rc;
         if (int rc = ctrl_tc_launch<EPI_STORE>(maps, p.J, U, R, p.ksplit, p.S, part, U, none, st, "ctrl_tc_gemm_kernel<dw>")) return rc;
     }
