@@ -5,8 +5,9 @@
 // lie (no concatenated copy); bias, 2*sigmoid(z)^2.3026 + 1e-7 and the scatter into c / a / H -- the fp32, contiguous
 // layouts the oscillator and noise kernels read -- happen in the GEMM epilogue.  Backward: dZ = g * msig'(z) with the
 // bias-gradient partials (one pass), dX = dZ W (same GEMM kernel, other operand layout), dW = dZ^T X (split over the
-// R dimension, partials summed in fixed order: deterministic).  FP32 FFMA throughout: the 1e-3 waveform bound against
-// the fp32 reference leaves no room for a tf32/bf16 product here.
+// R dimension, partials summed in fixed order: deterministic).  Two implementations of the products: FP32 FFMA tiles (first
+// half of this file; small R) and tcgen05 with bf16 x 3 operand splits (second half; R >= a few hundred) -- a plain tf32/bf16
+// product cannot hold the 1e-3 waveform bound against the fp32 reference, the split product is fp32-accurate.
 #include <algorithm>
 #include <climits>
 #include <cstdint>
