@@ -203,9 +203,9 @@ ctrl_gemm_kernel(Rows3 A, Rows3 B, int M, int N, int Kd, int ksplit, float* __re
     }
 }
 
-constexpr int DZ_ROWS = 32, DZ_TX = 128, DZ_TY = 4;
+constexpr int DZ_ROWS = 16, DZ_TX = 128, DZ_TY = 4;
 
-// dZ = g * msig'(z) for the three heads at once, plus per-row-tile column sums (bias-gradient partials).  A CTA owns 32 rows:
+// dZ = g * msig'(z) for the three heads at once, plus per-row-tile column sums (bias-gradient partials).  A CTA owns 16 rows:
 // thread (tx, ty) takes columns tx, tx + 128, ... of rows ty, ty + 4, ...; the four row groups' sums meet in shared memory in
 // a fixed order.  (First version: one thread per column walking the 32 rows, 4 warps per SM: 82 us at R = 5504, J = 376.)
 template <bool FAST>
@@ -260,6 +260,7 @@ ctrl_wgrad_finish_kernel(const float* __restrict__ part, int S, const float* __r
     for (size_t e = gid; e < total; e += (size_t)gridDim.x * blockDim.x) {
         const int j = (int)(e / U4), u = (int)(e % U4) * 4;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
         for (int s = 0; s < S; ++s) {
             const float4 v = *reinterpret_cast<const float4*>(part + s * plane + (size_t)j * U + u);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
@@ -267,11 +268,17 @@ ctrl_wgrad_finish_kernel(const float* __restrict__ part, int S, const float* __r
         float* dst = j < K ? gwc + (size_t)j * U : (j == K ? gwa : gwh + (size_t)(j - K - 1) * U);
         *reinterpret_cast<float4*>(dst + u) = acc;
     }
-    if (gid < (size_t)J) {
-        const int j = (int)gid;
+    // bias gradients: one warp per column, lane l sums tiles l, l + 32, ... and the lanes meet in a fixed tree (one thread per
+    // column walked all tiles in sequence: 172 dependent additions at R = 5504, most of this kernel's 13 us)
+    const size_t wid = gid >> 5;
+    if (wid < (size_t)J) {
+        const int j = (int)wid, lane = threadIdx.x & 31;
         float sum = 0.f;
-        for (int t = 0; t < tiles; ++t) sum += bpart[(size_t)t * ldz + j];
-        if (j < K) gbc[j] = sum; else if (j == K) gba[0] = sum; else gbh[j - K - 1] = sum;
+        for (int t = lane; t < tiles; t += 32) sum += bpart[(size_t)t * ldz + j];
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (lane == 0) {
+            if (j < K) gbc[j] = sum; else if (j == K) gba[0] = sum; else gbh[j - K - 1] = sum;
+        }
     }
 }
 
@@ -666,7 +673,7 @@ extern "C" int ddsp_ctrl_heads_backward(const float* x, const float* w_c, const 
     }
     const size_t total4 = (size_t)p.J * (U / 4);
     const int blocks = (int)std::min<size_t>((total4 + 255) / 256, 148 * 8);
-    ctrl_wgrad_finish_kernel<<<std::max(blocks, (p.J + 255) / 256), 256, 0, st>>>(part, p.S, bpart, p.tiles, p.ldz, gw_c, gw_a, gw_h,
+    ctrl_wgrad_finish_kernel<<<std::max(blocks, (p.J + 7) / 8), 256, 0, st>>>(part, p.S, bpart, p.tiles, p.ldz, gw_c, gw_a, gw_h,
                                                                                  gb_c, gb_a, gb_h, U, K, NB);
     DDSP_CHECK_LAUNCH("ctrl_wgrad_finish_kernel");
     return 0;
@@ -745,7 +752,7 @@ extern "C" int ddsp_ctrl_heads_backward_tc(const float* x, const float* w_c, con
     }
     const size_t total4 = (size_t)p.J * (U / 4);
     const int blocks = (int)std::min<size_t>((total4 + 255) / 256, 148 * 8);
-    ctrl_wgrad_finish_kernel<<<std::max(blocks, (p.J + 255) / 256), 256, 0, st>>>(part, p.S, bpart, p.tiles, p.ldz, gw_c, gw_a, gw_h,
+    ctrl_wgrad_finish_kernel<<<std::max(blocks, (p.J + 7) / 8), 256, 0, st>>>(part, p.S, bpart, p.tiles, p.ldz, gw_c, gw_a, gw_h,
                                                                                  gb_c, gb_a, gb_h, U, K, NB);
     DDSP_CHECK_LAUNCH("ctrl_wgrad_finish_kernel");
     return 0;

@@ -82,13 +82,16 @@ def mss(g):
 def features(g):
     n_fft, hop = 2048, 512
     ld = ops.loudness(_rnd(g, 2, 16000), _rnd(g, n_fft // 2 + 1), n_fft, hop)
-    U, K, NB, R = 512, 100, 65, 70
-    x = _rnd(g, R, U).requires_grad_(True)
-    ws = [_rnd(g, K, U, scale=0.05), _rnd(g, K), _rnd(g, 1, U, scale=0.05), _rnd(g, 1), _rnd(g, NB, U, scale=0.05), _rnd(g, NB)]
-    ws = [w.requires_grad_(True) for w in ws]
-    c, a, H = ops.controller_heads(x, *ws)
-    ((c * _rnd(g, R, K)).sum() + (a * _rnd(g, R, 1)).sum() + (H * _rnd(g, R, NB)).sum()).backward()
-    return [ld, c.detach(), a.detach(), H.detach(), x.grad] + [w.grad for w in ws]
+    out = [ld]
+    for U, K, NB, R in ((512, 100, 65, 70),          # FP32-pipe Controller tail
+                        (264, 100, 65, 300)):        # tcgen05 tail (R >= ops.CTRL_TC_MIN_ROWS): ragged in R, J and U (TMA zero fill)
+        x = _rnd(g, R, U).requires_grad_(True)
+        ws = [_rnd(g, K, U, scale=0.05), _rnd(g, K), _rnd(g, 1, U, scale=0.05), _rnd(g, 1), _rnd(g, NB, U, scale=0.05), _rnd(g, NB)]
+        ws = [w.requires_grad_(True) for w in ws]
+        c, a, H = ops.controller_heads(x, *ws)
+        ((c * _rnd(g, R, K)).sum() + (a * _rnd(g, R, 1)).sum() + (H * _rnd(g, R, NB)).sum()).backward()
+        out += [c.detach(), a.detach(), H.detach(), x.grad] + [w.grad for w in ws]
+    return out
 
 
 def fft(g):
