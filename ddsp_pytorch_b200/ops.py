@@ -3,6 +3,7 @@ all arithmetic happens in libddsp_b200.so.  Inputs may arrive in fp16/bf16 under
 runs ``precision=16``) and are cast to fp32 at this boundary."""
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -493,8 +494,9 @@ def loudness(signal: torch.Tensor, a_weight: torch.Tensor, n_fft: int, hop: int)
 
 
 # Rows from which the Controller tail runs on the tensor cores (csrc/ddsp_ctrl.cu: tcgen05 path); below it the split
-# pre-passes' launches cost more than the product.  0 disables the path (tests set it either way).
-CTRL_TC_MIN_ROWS = 256
+# pre-passes' launches cost more than the product.  0 disables the path (tests set it either way; the environment variable
+# DDSP_B200_CTRL_TC_MIN_ROWS sets it for a process).
+CTRL_TC_MIN_ROWS = int(os.environ.get("DDSP_B200_CTRL_TC_MIN_ROWS", "256"))
 
 
 def _ctrl_use_tensor_cores(R: int, U: int) -> bool:
