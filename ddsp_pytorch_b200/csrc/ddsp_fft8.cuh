@@ -15,6 +15,10 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#ifndef DDSP_FFT8_DERIVED_TWIDDLES
+#define DDSP_FFT8_DERIVED_TWIDDLES 1
+#endif
+
 namespace ddsp {
 
 template <typename T> struct cplx;
@@ -149,8 +153,21 @@ __device__ __forceinline__ void fft8_group(typename cplx<T>::type (&v)[8], typen
         const int k = t & (p - 1);
         if (s > 0) {
             const C* tb = fft8_table<T>(p, 8);
+#if DDSP_FFT8_DERIVED_TWIDDLES
+            // w^1, w^2, w^4 from the table, the other four as one product each of those (1 ulp): every table read is a
+            // wavefront (fp32) or two (fp64) on the L1 data pipe, which is what bounds the transform kernels
+            // (profiles/summary_r02.md section 9).  Measured against all seven from the table: c2c n = 2048 0.375 -> 0.355 ms,
+            // n = 4096 0.154 -> 0.150 ms, spectral loss cfg 5 0.631 -> 0.626 ms, reverb unchanged.
+            C w[8];
+            w[1] = __ldg(tb + k); w[2] = __ldg(tb + p + k); w[4] = __ldg(tb + 3 * p + k);
+            w[3] = c_mul_tw<false>(w[1], w[2]); w[5] = c_mul_tw<false>(w[1], w[4]);
+            w[6] = c_mul_tw<false>(w[2], w[4]); w[7] = c_mul_tw<false>(w[3], w[4]);
+#pragma unroll
+            for (int q = 1; q < 8; ++q) v[q] = c_mul_tw<INV>(v[q], w[q]);
+#else
 #pragma unroll
             for (int q = 1; q < 8; ++q) v[q] = c_mul_tw<INV>(v[q], __ldg(tb + (q - 1) * p + k));
+#endif
         }
         radix8<INV>(v);
         const bool last = (s == P::A - 1) && P::RL == 1;
