@@ -48,6 +48,7 @@ def parse_args():
     p.add_argument("--e2e-chunk", type=int, default=0, help="voices per chunk of the host pipeline (0: about 16 chunks per rank)")
     p.add_argument("--overlap-noise", action="store_true", help="issue the noise synthesiser on a second stream (its backward then overlaps the oscillator's)")
     p.add_argument("--equal-count-shards", action="store_true", help="shard by voice count instead of by work")
+    p.add_argument("--shard-of", default="", help="diagnostic: R/W = run alone, on one GPU, the shard rank R of a W-rank job would get")
     return p.parse_args()
 
 
@@ -264,7 +265,11 @@ def run_b200(args):
         ranges = [voice_shard(sh["B"], world, r) for r in range(world)]
     else:
         ranges = balanced_voice_shards(work.tolist(), world)
+    if args.shard_of:
+        er, ew = (int(v) for v in args.shard_of.split("/"))
+        ranges = [(balanced_voice_shards(work.tolist(), ew) if not args.equal_count_shards else [voice_shard(sh["B"], ew, r) for r in range(ew)])[er]]
     loads = [float(work[lo:hi].sum()) for lo, hi in ranges]
+    job_voices = sum(hi - lo for lo, hi in ranges)      # = sh["B"] except under --shard-of
     v_lo, v_hi = ranges[rank]
     Bl = v_hi - v_lo
 
@@ -359,7 +364,7 @@ def run_b200(args):
     my_ms = e0.elapsed_time(e1)
     ms = max_over_ranks(my_ms)
     clocks = sampler.stop(t_load0, time.time()) if sampler else None
-    value = sh["B"] * N * args.steps / (ms * 1e-3)
+    value = job_voices * N * args.steps / (ms * 1e-3)
     rank_ms = [v[0] / args.steps for v in gather_floats([my_ms])]
 
     # ---- end to end through the package's host pipeline: pinned host buffers in, pinned host buffers out ----------
@@ -398,7 +403,7 @@ def run_b200(args):
         barrier()
         copy_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
         per_rank = gather_floats([my_ems / args.steps, float(h2d), float(d2h), float(Bl), -2.0 if numa is None else float(numa)])
-        e2e = {"value": sh["B"] * N * args.steps / (ems * 1e-3), "unit": UNIT,
+        e2e = {"value": job_voices * N * args.steps / (ems * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(sum(r[1] for r in per_rank)), "d2h_bytes_per_step": int(sum(r[2] for r in per_rank)),
                "ms_per_step": ems / args.steps, "copy_only_ms_per_step": copy_ms,
                "frac_of_copy_roofline": copy_ms / (ems / args.steps),

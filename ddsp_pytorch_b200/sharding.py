@@ -23,14 +23,16 @@ def voice_shard(n_voices: int, world: int, rank: int) -> Tuple[int, int]:
     return lo, lo + base + (1 if rank < extra else 0)
 
 
-def voice_work(f0: torch.Tensor, n_harmonics: int, sample_rate: int, hop: int, per_sample_cost: float = 40.0) -> torch.Tensor:
+def voice_work(f0: torch.Tensor, n_harmonics: int, sample_rate: int, hop: int, per_sample_cost: float = 55.0) -> torch.Tensor:
     """f0 [B,T] or [B,T,1] (Hz) -> [B] float64 relative cost of one voice through oscillator + noise, forward + backward.
 
     Oscillator: harmonic k of frame t is active when k*f0 <= sample_rate//2 (harmonic_oscillator.py:31); a hop segment
     evaluates the larger active count of its two frames for each of its samples (half segments at both ends).  Everything
-    that does not depend on pitch -- the noise kernels (M + M*NB/hop flop per sample each way), prepare/finalize -- is
-    `per_sample_cost` harmonic-sample equivalents per audio sample (measured on B200 at cfg 4: 3.3e-13 s per active
-    harmonic-sample, 1.3e-11 s per sample for the rest)."""
+    that does not depend on pitch -- the noise kernels (M + M*NB/hop flop per sample each way), prepare/finalize, and the
+    oscillator kernels' own per-segment work (seeds, reductions, stores: about 37 harmonics' worth) -- is `per_sample_cost`
+    harmonic-sample equivalents per audio sample.  Fitted on B200 at cfg 4 by least squares over eleven shards of the 8-rank
+    job timed alone on one GPU (t = a * harmonic-samples + b * voices: a = 2.89e-13 s, b = 3.06 us per voice => 55;
+    residuals within 1.2 %; profiles/summary_r02.md section 11)."""
     f = f0.detach().reshape(f0.shape[0], f0.shape[1]).to(torch.float32).cpu()
     B, T = f.shape
     nyq = float(sample_rate // 2)
