@@ -326,8 +326,8 @@ struct Maps { CUtensorMap a[3], b[3]; };
 }  // namespace ctc
 
 template <int EPI>
-__global__ void __launch_bounds__(ctc::THREADS, 1)
-ctrl_tc_gemm_kernel(const __grid_constant__ ctc::Maps maps, int M, int N, int Kd, int ksplit, float* __restrict__ C, int ldc, HeadsOut ho) {
+__device__ __forceinline__ void ctrl_tc_tile(const ctc::Maps& maps, int M, int N, int Kd, int ksplit, float* __restrict__ C, int ldc,
+                                             const HeadsOut& ho, int bx, int by, int bz) {
     using namespace ctc;
     extern __shared__ unsigned char ctc_raw[];
     unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)ctc_raw + 1023) & ~(uintptr_t)1023);
@@ -338,8 +338,8 @@ ctrl_tc_gemm_kernel(const __grid_constant__ ctc::Maps maps, int M, int N, int Kd
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-    const int kbeg = blockIdx.z * ksplit, kend = min(Kd, kbeg + ksplit);
+    const int m0 = bx * BM, n0 = by * BN;
+    const int kbeg = bz * ksplit, kend = min(Kd, kbeg + ksplit);
     const int nk = (kend - kbeg + BK - 1) / BK;          // >= 1 (host)
     const int nk0 = (nk + 1) / 2;                        // panels of the first half of K
 
@@ -443,7 +443,7 @@ ctrl_tc_gemm_kernel(const __grid_constant__ ctc::Maps maps, int M, int N, int Kd
             if (col >= N) continue;
             const float acc = tile[(size_t)r * TILE_LD + lane + 32 * i];
             if (EPI == EPI_STORE) {
-                C[(size_t)blockIdx.z * M * ldc + (size_t)m * ldc + col] = acc;
+                C[(size_t)bz * M * ldc + (size_t)m * ldc + col] = acc;
             } else {
                 float z;
                 if (col < ho.K) {
@@ -460,6 +460,30 @@ ctrl_tc_gemm_kernel(const __grid_constant__ ctc::Maps maps, int M, int N, int Kd
             }
         }
     }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(ctc::THREADS, 1)
+ctrl_tc_gemm_kernel(const __grid_constant__ ctc::Maps maps, int M, int N, int Kd, int ksplit, float* __restrict__ C, int ldc, HeadsOut ho) {
+    ctrl_tc_tile<EPI>(maps, M, N, Kd, ksplit, C, ldc, ho, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// Two independent products in one launch (the backward's dX and dW): the second one's CTAs fill what the first leaves of its
+// last wave -- 172 + 120 CTAs are two waves of 148 SMs, launched apart they were three.
+struct TcProblem {
+    ctc::Maps maps;
+    int M, N, Kd, ksplit, ldc;
+    float* C;
+    unsigned gx, gy, gz;
+};
+__global__ void __launch_bounds__(ctc::THREADS, 1)
+ctrl_tc_gemm2_kernel(const __grid_constant__ TcProblem p0, const __grid_constant__ TcProblem p1) {
+    const unsigned n0 = p0.gx * p0.gy * p0.gz;
+    const bool first = blockIdx.x < n0;
+    const TcProblem& p = first ? p0 : p1;
+    const unsigned b = first ? blockIdx.x : blockIdx.x - n0;
+    const HeadsOut none{};
+    ctrl_tc_tile<EPI_STORE>(p.maps, p.M, p.N, p.Kd, p.ksplit, p.C, p.ldc, none, (int)(b % p.gx), (int)((b / p.gx) % p.gy), (int)(b / (p.gx * p.gy)));
 }
 
 // One launch splits up to three matrices (fewer launches matter: the path is host-bound in eager mode at the shapes it serves).
@@ -550,7 +574,7 @@ static int launch_split_transpose(const SplitJob* jb, int n, cudaStream_t st) {
 }
 
 struct CtrlTcPlan {
-    int J, ldz, J8, R8, tiles, S, ksplit;
+    int J, ldz, J8, R8, tiles, S, ksplit, S2, ksplit2;      // S2 / ksplit2: dW's K split when it shares a launch with dX
     // byte offsets into the workspace
     size_t off_xp, off_wp;                                      // forward: x and W planes, K-major in U
     size_t off_part, off_bpart, off_dz, off_dzp, off_wt, off_dzt, off_xt;     // backward
@@ -564,16 +588,24 @@ static CtrlTcPlan ctrl_tc_plan(int R, int U, int K, int NB) {
     p.R8 = (R + 7) & ~7;
     p.tiles = (R + DZ_ROWS - 1) / DZ_ROWS;
     const int ctas = ((p.J + ctc::BM - 1) / ctc::BM) * ((U + ctc::BN - 1) / ctc::BN);
-    int S = std::max(1, std::min(148 / std::max(ctas, 1), (R + 127) / 128));
-    p.ksplit = (((R + S - 1) / S) + ctc::BK - 1) / ctc::BK * ctc::BK;
-    p.S = (R + p.ksplit - 1) / p.ksplit;
+    auto split = [&](int s_want, int& ksplit, int& S) {
+        s_want = std::max(1, std::min(s_want, (R + 127) / 128));
+        ksplit = (((R + s_want - 1) / s_want) + ctc::BK - 1) / ctc::BK * ctc::BK;
+        S = (R + ksplit - 1) / ksplit;
+    };
+    split(148 / std::max(ctas, 1), p.ksplit, p.S);                       // dW alone: one wave
+    // dW launched with dX: as many K splits as fit the SMs dX leaves free in its last wave (one more wave if that is too few)
+    const int n_dx = ((R + ctc::BM - 1) / ctc::BM) * ((U + ctc::BN - 1) / ctc::BN);
+    int free_sms = (n_dx + 147) / 148 * 148 - n_dx;
+    if (free_sms < ctas) free_sms += 148;
+    split(free_sms / std::max(ctas, 1), p.ksplit2, p.S2);
     const size_t h = sizeof(__nv_bfloat16);
     size_t off = 0;
     p.off_xp = off; off += align_up(3 * h * (size_t)R * U, 1024);
     p.off_wp = off; off += align_up(3 * h * (size_t)p.J * U, 1024);
     p.fwd_bytes = off;
     off = 0;
-    p.off_part = off;  off += align_up(sizeof(float) * (size_t)p.S * p.J * U, 1024);
+    p.off_part = off;  off += align_up(sizeof(float) * (size_t)std::max(p.S, p.S2) * p.J * U, 1024);
     p.off_bpart = off; off += align_up(sizeof(float) * (size_t)p.tiles * p.ldz, 1024);
     p.off_dz = off;    off += align_up(sizeof(float) * (size_t)R * p.ldz, 1024);
     p.off_dzp = off;   off += align_up(3 * h * (size_t)R * p.J8, 1024);
@@ -741,18 +773,30 @@ extern "C" int ddsp_ctrl_heads_backward_tc(const float* x, const float* w_c, con
                                 split_transpose_job(W, p.J, U, wt, p.J8)};
         if (int rc = launch_split_transpose(jb, gx ? 3 : 2, st)) return rc;
     }
-    if (gx) {       // gx[R,U] = dZ[R,J] * Wcat[J,U]: A = dZ (K-major in J, planes written by ctrl_dz_kernel), B = Wcat^T [U,J]
-        if (int rc = ctrl_tc_maps(maps, dzp, (uint64_t)R, (uint64_t)p.J8, wt, (uint64_t)U, (uint64_t)p.J8, (uint64_t)p.J)) return rc;
-        if (int rc = ctrl_tc_launch<EPI_STORE>(maps, R, U, p.J, (p.J + ctc::BK - 1) / ctc::BK * ctc::BK, 1, gx, U, none, st, "ctrl_tc_gemm_kernel<dx>"))
-            return rc;
-    }
-    {               // partial[s][J,U] = dZ[rows of split s]^T * X[rows of split s]: A = dZ^T [J,R], B = X^T [U,R]
+    int S_used = p.S;
+    if (gx) {       // gx[R,U] = dZ[R,J] Wcat[J,U] (A = dZ, K-major in J: planes written by ctrl_dz_kernel; B = Wcat^T [U,J]) and, in
+                    // the same launch, partial[s][J,U] = dZ[rows of split s]^T X[rows of split s] (A = dZ^T [J,R], B = X^T [U,R])
+        TcProblem dx{}, dw{};
+        if (int rc = ctrl_tc_maps(dx.maps, dzp, (uint64_t)R, (uint64_t)p.J8, wt, (uint64_t)U, (uint64_t)p.J8, (uint64_t)p.J)) return rc;
+        if (int rc = ctrl_tc_maps(dw.maps, dzt, (uint64_t)p.J, (uint64_t)p.R8, xt, (uint64_t)U, (uint64_t)p.R8, (uint64_t)R)) return rc;
+        dx.M = R; dx.N = U; dx.Kd = p.J; dx.ksplit = (p.J + ctc::BK - 1) / ctc::BK * ctc::BK; dx.ldc = U; dx.C = gx;
+        dx.gx = (unsigned)((R + ctc::BM - 1) / ctc::BM); dx.gy = (unsigned)((U + ctc::BN - 1) / ctc::BN); dx.gz = 1;
+        dw.M = p.J; dw.N = U; dw.Kd = R; dw.ksplit = p.ksplit2; dw.ldc = U; dw.C = part;
+        dw.gx = (unsigned)((p.J + ctc::BM - 1) / ctc::BM); dw.gy = (unsigned)((U + ctc::BN - 1) / ctc::BN); dw.gz = (unsigned)p.S2;
+        S_used = p.S2;
+        cudaError_t e = cudaFuncSetAttribute(ctrl_tc_gemm2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctc::SMEM);
+        DDSP_REQUIRE(e == cudaSuccess, "ctrl_tc_gemm2_kernel: cannot reserve %zu B of shared memory: %s", (size_t)ctc::SMEM, cudaGetErrorString(e));
+        const unsigned long long blocks2 = (unsigned long long)dx.gx * dx.gy + (unsigned long long)dw.gx * dw.gy * dw.gz;
+        DDSP_REQUIRE(blocks2 <= 0x7fffffffull, "ctrl_tc_gemm2_kernel: matrix too large");
+        ctrl_tc_gemm2_kernel<<<(unsigned)blocks2, ctc::THREADS, ctc::SMEM, st>>>(dx, dw);
+        DDSP_CHECK_LAUNCH("ctrl_tc_gemm2_kernel");
+    } else {        // partial[s][J,U] = dZ[rows of split s]^T * X[rows of split s]: A = dZ^T [J,R], B = X^T [U,R]
         if (int rc = ctrl_tc_maps(maps, dzt, (uint64_t)p.J, (uint64_t)p.R8, xt, (uint64_t)U, (uint64_t)p.R8, (uint64_t)R)) return rc;
         if (int rc = ctrl_tc_launch<EPI_STORE>(maps, p.J, U, R, p.ksplit, p.S, part, U, none, st, "ctrl_tc_gemm_kernel<dw>")) return rc;
     }
     const size_t total4 = (size_t)p.J * (U / 4);
     const int blocks = (int)std::min<size_t>((total4 + 255) / 256, 148 * 8);
-    ctrl_wgrad_finish_kernel<<<std::max(blocks, (p.J + 7) / 8), 256, 0, st>>>(part, p.S, bpart, p.tiles, p.ldz, gw_c, gw_a, gw_h,
+    ctrl_wgrad_finish_kernel<<<std::max(blocks, (p.J + 7) / 8), 256, 0, st>>>(part, S_used, bpart, p.tiles, p.ldz, gw_c, gw_a, gw_h,
                                                                                  gb_c, gb_a, gb_h, U, K, NB);
     DDSP_CHECK_LAUNCH("ctrl_wgrad_finish_kernel");
     return 0;
