@@ -127,3 +127,34 @@ def test_controller_uses_fused_tail_and_matches_torch_tail():
     ctl.zero_grad(set_to_none=True)
     ctl(batch)["c"].sum().backward()
     assert ctl.dense_filter.weight.grad.abs().max() == 0 and ctl.dense_harmonic.weight.grad.abs().max() > 0
+
+@pytest.mark.gpu
+def test_tensor_core_tail_random_shapes(monkeypatch):
+    """Twenty-four random (R, U, K, NB) through the tcgen05 kernels against fp64 torch: ragged tiles in every dimension (R, J and U
+    not multiples of 128 / 128 / 64), K-split counts from 1 up, single rows, J below one tile and above three."""
+    from ddsp_pytorch_b200 import ops
+    monkeypatch.setattr(ops, "CTRL_TC_MIN_ROWS", 1)
+    rng = np.random.default_rng(2025)
+    dev = "cuda"
+    for case in range(24):
+        R = int(rng.choice([1, 7, 127, 128, 129, 300, 777, 1500, 2049]))
+        U = int(rng.choice([64, 72, 128, 200, 512, 520]))
+        K = int(rng.integers(1, 300))
+        NB = int(rng.integers(1, 260))
+        torch.manual_seed(case)
+        x = torch.randn(R, U, device=dev)
+        ps = [torch.randn(K, U, device=dev) * 0.1, torch.randn(K, device=dev), torch.randn(1, U, device=dev) * 0.1,
+              torch.randn(1, device=dev), torch.randn(NB, U, device=dev) * 0.1, torch.randn(NB, device=dev)]
+        gs = [torch.randn(R, K, device=dev), torch.randn(R, 1, device=dev), torch.randn(R, NB, device=dev)]
+        assert ops._ctrl_use_tensor_cores(R, U)
+        outs, gx, gps = _run_kernel(x, ps, gs)
+        xd = x.double().requires_grad_(True)
+        pd = [p.double().requires_grad_(True) for p in ps]
+        want = O.controller_heads(xd, *pd)
+        (sum((w * g.double()).sum() for w, g in zip(want, gs))).backward()
+        tag = f"case {case}: R={R} U={U} K={K} NB={NB}"
+        for got, w in zip(outs, want):
+            assert float(((got.double() - w.detach()).abs() / (w.detach().abs() + 1e-6)).max()) <= 1e-4, tag
+        assert _rel(gx, xd.grad) <= 2e-5, tag
+        for gp, p in zip(gps, pd):
+            assert _rel(gp, p.grad) <= 2e-5, tag
