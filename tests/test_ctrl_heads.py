@@ -48,8 +48,13 @@ def _rel(got, want):
 
 
 @pytest.mark.gpu
-def test_kernel_matches_reference_fixture():
+@pytest.mark.parametrize("path", ["ffma", "tcgen05"])
+def test_kernel_matches_reference_fixture(path, monkeypatch):
+    """Both product paths against the fixture the reference's own Controller produced (150 rows, U = 64, J = 35), same bounds."""
+    from ddsp_pytorch_b200 import ops
+    monkeypatch.setattr(ops, "CTRL_TC_MIN_ROWS", 0 if path == "ffma" else 1)
     g, t = _gold(torch.float32, "cuda")
+    assert ops._ctrl_use_tensor_cores(150, 64) == (path == "tcgen05")
     (c, a, H), gx, gps = _run_kernel(t("x"), [t(k) for k in PARAMS], [t("g_c"), t("g_a"), t("g_h")])
     _, t64 = _gold(torch.float64, "cuda")
     for got, key in ((c, "c"), (a, "a"), (H, "H")):
