@@ -203,6 +203,55 @@ ctrl_gemm_kernel(Rows3 A, Rows3 B, int M, int N, int Kd, int ksplit, float* __re
     }
 }
 
+// Forward for a handful of rows (the real-time decoder: one block of 1-16 frames, rt/synth.py:21-55): the tiled product above
+// puts 6-12 CTAs through 32 barrier-separated K steps (49 us for any R <= 128); here one warp owns one output column for all
+// rows -- lanes stride over U in float4, x lives in shared memory, one shuffle tree per row -- and the launch takes a few us.
+constexpr int SMALL_ROWS = 16, SMALL_WARPS = 8;
+__global__ void __launch_bounds__(32 * SMALL_WARPS)
+ctrl_heads_small_kernel(const float* __restrict__ x, Rows3 W, int R, int U, int J, HeadsOut ho) {
+    extern __shared__ __align__(16) float xs[];                     // [R][U]
+    for (int i = threadIdx.x * 4; i < R * U; i += 32 * SMALL_WARPS * 4)
+        *reinterpret_cast<float4*>(xs + i) = *reinterpret_cast<const float4*>(x + i);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int col = blockIdx.x * SMALL_WARPS + (threadIdx.x >> 5);
+    if (col >= J) return;
+    const float* wr = W.row(col);
+    float acc[SMALL_ROWS];
+#pragma unroll
+    for (int r = 0; r < SMALL_ROWS; ++r) acc[r] = 0.f;
+    for (int u = lane * 4; u < U; u += 128) {
+        const float4 w = *reinterpret_cast<const float4*>(wr + u);
+#pragma unroll
+        for (int r = 0; r < SMALL_ROWS; ++r) {
+            if (r < R) {
+                const float4 v = *reinterpret_cast<const float4*>(xs + (size_t)r * U + u);
+                acc[r] = fmaf(v.w, w.w, fmaf(v.z, w.z, fmaf(v.y, w.y, fmaf(v.x, w.x, acc[r]))));
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < SMALL_ROWS; ++r) {
+        if (r >= R) break;
+        float a = acc[r];
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) {
+            float z;
+            if (col < ho.K) {
+                z = a + ho.bias[0][col];
+                ho.c[(size_t)r * ho.K + col] = msig(z);
+            } else if (col == ho.K) {
+                z = a + ho.bias[1][0];
+                ho.a[r] = msig(z);
+            } else {
+                z = a + ho.bias[2][col - ho.K - 1];
+                ho.H[(size_t)r * ho.NB + (col - ho.K - 1)] = msig(z);
+            }
+            if (ho.z) ho.z[(size_t)r * ho.ldz + col] = z;
+        }
+    }
+}
+
 constexpr int DZ_ROWS = 16, DZ_TX = 128, DZ_TY = 4;
 
 // dZ = g * msig'(z) for the three heads at once, plus per-row-tile column sums (bias-gradient partials).  A CTA owns 16 rows:
@@ -663,6 +712,12 @@ extern "C" int ddsp_ctrl_heads_forward(const float* x, const float* w_c, const f
     Rows3 A = rows_plain(x, U);
     Rows3 B{{w_c, w_a, w_h}, K, K + 1, U};
     HeadsOut ho{{b_c, b_a, b_h}, c, a, H, z, K, NB, ddsp_ctrl_heads_ldz(K, NB)};
+    if (R <= SMALL_ROWS && (size_t)R * U * sizeof(float) <= 48 * 1024) {
+        ctrl_heads_small_kernel<<<(J + SMALL_WARPS - 1) / SMALL_WARPS, 32 * SMALL_WARPS, (size_t)R * U * sizeof(float),
+                                  static_cast<cudaStream_t>(stream)>>>(x, B, R, U, J, ho);
+        DDSP_CHECK_LAUNCH("ctrl_heads_small_kernel");
+        return 0;
+    }
     dim3 grid((R + G_BM - 1) / G_BM, (J + G_BN - 1) / G_BN, 1);
     DDSP_REQUIRE(grid.y <= 65535, "ddsp_ctrl_heads_forward: K + NB too large");
     ctrl_gemm_kernel<true, true, EPI_HEADS><<<grid, G_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(A, B, R, J, U, U, nullptr, 0, ho);

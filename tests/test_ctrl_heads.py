@@ -76,6 +76,9 @@ def test_kernel_matches_reference_fixture(path, monkeypatch):
                                        (1, 1, 512, 180, 195),       # rt/synth.py: one frame
                                        (2, 37, 24, 3, 2),           # ragged everything
                                        (1, 300, 128, 256, 65),
+                                       (1, 4, 512, 180, 195),       # rt/synth.py: a block of four frames (small-R forward kernel)
+                                       (2, 8, 64, 21, 13),          # 16 rows: the small kernel's last size
+                                       (1, 17, 128, 5, 3),          # 17 rows: the tiled kernel's first
                                        (4, 100, 64, 3, 2),          # J = 6: far fewer output columns than a tile
                                        (3, 130, 72, 50, 20)])       # U not a multiple of the 64-wide K panel
 @pytest.mark.parametrize("path", ["ffma", "tcgen05", "auto"])
