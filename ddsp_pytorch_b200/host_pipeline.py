@@ -176,6 +176,7 @@ class HostSynthPipeline:
                     done = torch.cuda.Event()
                     done.record(self.s_out)
                     out_free[slot] = done
-        self.launches_per_step = int(_lib.load().ddsp_launch_count() - count0)
+        if not copy_only:                               # (the copy-only measurement launches nothing and must not reset the count)
+            self.launches_per_step = int(_lib.load().ddsp_launch_count() - count0)
         if done is not None:
             done.synchronize()                          # the host now owns the audio and the gradients
