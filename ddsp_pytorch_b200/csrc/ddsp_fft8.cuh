@@ -10,7 +10,8 @@
 //   * exchange buffer: n complex values per group with a padded index (fft8_pad) -- with that padding the scattered
 //     writes of every stage and the unit-stride reads are bank-conflict free;
 //   * twiddles: per-stage tables T[q-1][k] = exp(-+2 pi i q k / (r p)) (k < p, q < r) in global memory, rounded
-//     from fp64, read through L1 with unit stride across the group (tables are shared by all transforms on the SM);
+//     from fp64, read through L1 with unit stride across the group (tables are shared by all transforms on the SM); a radix-8
+//     stage reads w, w^2, w^4 and forms the other four as one product each (DDSP_FFT8_DERIVED_TWIDDLES);
 //   * T = float or double (the spectral loss runs its predicted frames in fp64, see ddsp_mss.cu).
 #pragma once
 #include <cuda_runtime.h>
