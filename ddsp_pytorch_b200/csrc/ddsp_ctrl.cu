@@ -203,13 +203,17 @@ ctrl_gemm_kernel(Rows3 A, Rows3 B, int M, int N, int Kd, int ksplit, float* __re
     }
 }
 
-// Forward for a handful of rows (the real-time decoder: one block of 1-16 frames, rt/synth.py:21-55): the tiled product above
-// puts 6-12 CTAs through 32 barrier-separated K steps (49 us for any R <= 128); here one warp owns one output column for all
-// rows -- lanes stride over U in float4, x lives in shared memory, one shuffle tree per row -- and the launch takes a few us.
-constexpr int SMALL_ROWS = 16, SMALL_WARPS = 8;
+// Forward for up to 255 rows (the real-time decoder: one block of 1-16 frames, rt/synth.py:21-55): the tiled product above
+// puts 6-12 CTAs through 32 barrier-separated K steps (49 us for any R <= 128); here one warp owns one output column for a
+// group of 16 rows -- lanes stride over U in float4, the group's x lives in shared memory, one shuffle tree per row: 4 us at
+// R = 1, 6 at R = 4, 10 at R = 16-64, 14 at R = 128.
+constexpr int SMALL_ROWS = 16, SMALL_WARPS = 8, SMALL_MAX_ROWS = 255;     // rows per CTA, columns per CTA, largest R served (the tensor-core path starts at 256)
 __global__ void __launch_bounds__(32 * SMALL_WARPS)
 ctrl_heads_small_kernel(const float* __restrict__ x, Rows3 W, int R, int U, int J, HeadsOut ho) {
-    extern __shared__ __align__(16) float xs[];                     // [R][U]
+    extern __shared__ __align__(16) float xs[];                     // [rows of this group][U]
+    const int rbase = blockIdx.y * SMALL_ROWS;                      // blockIdx.y: group of SMALL_ROWS rows
+    x += (size_t)rbase * U;
+    R = min(SMALL_ROWS, R - rbase);
     for (int i = threadIdx.x * 4; i < R * U; i += 32 * SMALL_WARPS * 4)
         *reinterpret_cast<float4*>(xs + i) = *reinterpret_cast<const float4*>(x + i);
     __syncthreads();
@@ -236,18 +240,19 @@ ctrl_heads_small_kernel(const float* __restrict__ x, Rows3 W, int R, int U, int 
         float a = acc[r];
         for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
         if (lane == 0) {
+            const size_t m = (size_t)rbase + r;
             float z;
             if (col < ho.K) {
                 z = a + ho.bias[0][col];
-                ho.c[(size_t)r * ho.K + col] = msig(z);
+                ho.c[m * ho.K + col] = msig(z);
             } else if (col == ho.K) {
                 z = a + ho.bias[1][0];
-                ho.a[r] = msig(z);
+                ho.a[m] = msig(z);
             } else {
                 z = a + ho.bias[2][col - ho.K - 1];
-                ho.H[(size_t)r * ho.NB + (col - ho.K - 1)] = msig(z);
+                ho.H[m * ho.NB + (col - ho.K - 1)] = msig(z);
             }
-            if (ho.z) ho.z[(size_t)r * ho.ldz + col] = z;
+            if (ho.z) ho.z[m * ho.ldz + col] = z;
         }
     }
 }
@@ -712,9 +717,10 @@ extern "C" int ddsp_ctrl_heads_forward(const float* x, const float* w_c, const f
     Rows3 A = rows_plain(x, U);
     Rows3 B{{w_c, w_a, w_h}, K, K + 1, U};
     HeadsOut ho{{b_c, b_a, b_h}, c, a, H, z, K, NB, ddsp_ctrl_heads_ldz(K, NB)};
-    if (R <= SMALL_ROWS && (size_t)R * U * sizeof(float) <= 48 * 1024) {
-        ctrl_heads_small_kernel<<<(J + SMALL_WARPS - 1) / SMALL_WARPS, 32 * SMALL_WARPS, (size_t)R * U * sizeof(float),
-                                  static_cast<cudaStream_t>(stream)>>>(x, B, R, U, J, ho);
+    if (R <= SMALL_MAX_ROWS && (size_t)SMALL_ROWS * U * sizeof(float) <= 48 * 1024) {
+        const int rows = std::min(R, SMALL_ROWS);
+        ctrl_heads_small_kernel<<<dim3((J + SMALL_WARPS - 1) / SMALL_WARPS, (R + SMALL_ROWS - 1) / SMALL_ROWS), 32 * SMALL_WARPS,
+                                  (size_t)rows * U * sizeof(float), static_cast<cudaStream_t>(stream)>>>(x, B, R, U, J, ho);
         DDSP_CHECK_LAUNCH("ctrl_heads_small_kernel");
         return 0;
     }
